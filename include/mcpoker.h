@@ -1,0 +1,125 @@
+/*
+ * mcpoker.h -- C ABI of libmcpoker.so, the B200 (sm_100a) engine behind the reference's hand-ranking /
+ * showdown path.  Only ints, pointers to primitive arrays and sizes cross this boundary (JNA / Panama /
+ * ctypes friendly: no structs by value, no callbacks, no torch types).
+ *
+ * What each entry point replaces in the reference (/root/reference/src/montecarlo/...):
+ *   mc_eval_cards        hand_evaluator.clj:112-133 `evaluator` (5 cards) and :162-172 `player->hand-value`
+ *                        (5/6/7 cards = flop/turn/river), one hand
+ *   mc_eval7_batch[_dev] the same, lifted over a batch (`(map #(player->hand-value board %) ids)`,
+ *                        gameplay.clj:127-128)
+ *   mc_showdown          gameplay.clj:127-132 `end-game` ranking + :118-120 `group-winners`
+ *   mc_enumerate7*       player->hand-value over every C(52,7) hand (BASELINE config 2)
+ *   mc_equity_exhaustive* end-game ranking over every completion of the board (config 3)
+ *   mc_equity_mc*        deal (board.clj:148 shuffle, gameplay.clj:63-75 deal-hand, :41-54 flop/turn/river)
+ *                        + end-game ranking per trial (config 4)
+ *   mc_preflop_matrix    config 5
+ *
+ * Encodings
+ *   card id   13*suit + (rank-2): index in COMPLETE-DECK (card.clj:10-13); suit 0..3 = hearts, diamonds,
+ *             spades, clubs; rank 2..14
+ *   card set  uint64 mask, bit (16*suit + rank); ranks 1..14 are accepted by the evaluation entry points
+ *             (rank 1 exists only in the reference's tests); enumeration / equity use the 52-card deck
+ *   key       uint32, MC_KEY_NIBBLE (default):  cat<<20 | r1<<16 | r2<<12 | r3<<8 | r4<<4 | r5 where
+ *             r1..r5 = (concat hit kick) of the Clojure value [cat hit kick] (hand_evaluator.clj:100-133).
+ *             Unsigned order of keys == clojure.core/compare order of the values; equal keys <=> `=` values.
+ *             hit lengths by cat 0..8: 5,2,4,3,5,5,5,4,5.   0xFFFFFFFF marks an invalid input hand.
+ *             MC_KEY_PACKED: cat<<28 | P<<14 | S with P, S 14-bit rank sets (bit r-1): same order, decodes
+ *             to the same value (mc_key_packed_to_nibble); it is what the equity kernels compare internally.
+ *
+ * Every function returns 0 (MC_OK) or a negative MC_ERR_*; mc_last_error() holds a thread-local message.
+ * The caller owns every buffer it passes; the library owns device memory, streams and tables.  All entry
+ * points are thread-safe (calls that touch the same device are serialised inside the library).  There is
+ * no CPU fallback: without a usable sm_100 device every compute call fails with MC_ERR_NO_DEVICE.
+ */
+#ifndef MCPOKER_H
+#define MCPOKER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MC_OK               0
+#define MC_ERR_INVALID     -1   /* bad argument (the reference would throw or mis-evaluate) */
+#define MC_ERR_NOT_INIT    -2
+#define MC_ERR_CUDA        -3
+#define MC_ERR_NO_DEVICE   -4
+#define MC_ERR_TOO_FEW     -5   /* fewer than 5 cards: reference raises ArityException */
+
+#define MC_KEY_NIBBLE       0
+#define MC_KEY_PACKED       1
+#define MC_KEY_INVALID      0xFFFFFFFFu
+
+#define MC_MAX_SEATS        9
+#define MC_N_CLASSES        169
+
+/* ---- lifecycle ---------------------------------------------------------------------------------- */
+int  mc_init(int n_gpus /* 0 = all visible */, unsigned flags);
+int  mc_init_devices(const int *device_ids, int n);      /* one process per GPU: pass {LOCAL_RANK} */
+void mc_shutdown(void);
+int  mc_device_count(void);                               /* devices this library instance drives */
+const char *mc_last_error(void);
+int  mc_abi_version(void);
+
+/* ---- pure host helpers (bit shuffling only, no evaluation) ------------------------------------- */
+uint64_t mc_card_bit(int card_id);                                        /* 0 on bad id */
+uint32_t mc_key_packed_to_nibble(uint32_t packed_key);
+int  mc_key_decode(uint32_t nibble_key, int32_t *cat, int32_t hit[5], int32_t *n_hit,
+                   int32_t kick[5], int32_t *n_kick);                     /* -> [cat hit kick] */
+
+/* ---- evaluation (K1) ----------------------------------------------------------------------------- */
+int  mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards /* 5..7 */, uint32_t *key);
+int  mc_eval7_batch(const uint64_t *masks, size_t n, uint32_t *keys);                 /* host buffers */
+int  mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_format);
+int  mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void *stream);
+int  mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream);
+int  mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
+                 uint32_t *keys, uint32_t *winner_bitmask);
+/* full end-game grouping: group_of[seat] = index of its tie group, 0 = best (gameplay.clj:118-120) */
+int  mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
+                        uint32_t *keys, int32_t *group_of, int32_t *n_groups);
+
+/* ---- synthetic inputs (BASELINE config 1: Philox-seeded random hands, identical on CPU and GPU) --- */
+int  mc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *masks);
+int  mc_random_hands_dev(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks, void *stream);
+
+/* ---- exhaustive enumeration (K2) ---------------------------------------------------------------- */
+/* combination index = colex rank over card ids: sum_i C(c_i, i+1), c_0 < ... < c_6 */
+int  mc_enumerate7(uint64_t hist[9], uint64_t *key_sum /* nullable; sum of nibble keys */);
+int  mc_enumerate7_range(uint64_t first, uint64_t count, uint64_t hist[9], uint64_t *key_sum);
+/* d_out: 10 x uint64 on the current device = hist[0..8], key_sum; accumulated into (zero it first) */
+int  mc_enumerate7_dev(uint64_t first, uint64_t count, uint64_t *d_out, void *stream);
+
+/* ---- exhaustive equity (K3) --------------------------------------------------------------------- */
+int  mc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                          int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_boards);
+int  mc_equity_exhaustive_range(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                                uint64_t first_board, uint64_t n_boards_in,
+                                int64_t *win, int64_t *tie, int64_t *loss);
+/* d_counts: 3*MC_MAX_SEATS int64 on the current device, [win[9] tie[9] loss[9]], accumulated into */
+int  mc_equity_exhaustive_dev(const uint64_t *hole_masks /* host */, int n_seats, uint64_t board_mask,
+                              uint64_t dead_mask, uint64_t first_board, uint64_t n_boards_in,
+                              int64_t *d_counts, void *stream);
+
+/* ---- Monte Carlo equity (K4) -------------------------------------------------------------------- */
+/* hole mask 0 = random seat.  Trial t depends only on (seed, t): any split of [first, first+n) over
+ * devices / processes / calls sums to the same counts. */
+int  mc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                  uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                  int64_t *win, int64_t *tie, int64_t *loss);
+int  mc_equity_mc_dev(const uint64_t *hole_masks /* host */, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                      uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                      int64_t *d_counts /* 27 int64, accumulated into */, void *stream);
+
+/* ---- 169 x 169 preflop matrix (K5) -------------------------------------------------------------- */
+/* class id: x = rank-2; pair 13x+x; suited (hi>lo) 13*hi+lo; offsuit 13*lo+hi.  wtl[a][b] = {win,tie,loss} of a */
+int  mc_preflop_matrix(int64_t *wtl /* 169*169*3 */);
+int  mc_preflop_cells(const int32_t *class_a, const int32_t *class_b, int n_cells, int64_t *wtl /* n*3 */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,577 @@
+// capi.cu -- the extern "C" boundary of libmcpoker.so (include/mcpoker.h).  Host-side plumbing only:
+// argument checks, device contexts, staging pipelines, range sharding over the devices of one process and
+// the final sum of the per-device int64 counts.  All hand evaluation happens in kernels.cu; there is no CPU
+// evaluation path in this library.
+#include "../../include/mcpoker.h"
+#include "eval.cuh"
+#include "kernels.cuh"
+#include "philox.cuh"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace mcp;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string &msg) { g_err = msg; return code; }
+int cuda_fail(cudaError_t e, const char *what) {
+    return fail(MC_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return cuda_fail(e_, #x); } while (0)
+
+constexpr int N_SLOTS = 3;
+constexpr size_t SLOT_HANDS = 1u << 22;           // 4 Mi hands per pipeline stage: 32 MiB in, 16 MiB out
+constexpr int SMALL_WORDS = 64;
+
+struct DevCtx {
+    int device = -1;
+    DeviceInfo info{};
+    std::mutex mu;
+    cudaStream_t stream = nullptr;                // small jobs
+    cudaStream_t slot_stream[N_SLOTS] = {};
+    uint64_t *d_in[N_SLOTS] = {};
+    uint32_t *d_out[N_SLOTS] = {};
+    unsigned long long *d_small = nullptr;        // SMALL_WORDS x u64 scratch
+    unsigned long long *h_small = nullptr;        // pinned mirror
+    Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
+    long long *d_wtl = nullptr;
+
+    ~DevCtx() {
+        if (device < 0) return;
+        cudaSetDevice(device);
+        for (int i = 0; i < N_SLOTS; i++) {
+            if (d_in[i]) cudaFree(d_in[i]);
+            if (d_out[i]) cudaFree(d_out[i]);
+            if (slot_stream[i]) cudaStreamDestroy(slot_stream[i]);
+        }
+        if (d_small) cudaFree(d_small);
+        if (h_small) cudaFreeHost(h_small);
+        if (d_matchups) cudaFree(d_matchups);
+        if (d_wtl) cudaFree(d_wtl);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+std::mutex g_mu;
+std::vector<std::unique_ptr<DevCtx>> g_ctx;
+
+int make_info(int dev, DeviceInfo *out) {
+    int major = 0, sms = 0;
+    CU(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (major != 10) return fail(MC_ERR_NO_DEVICE, "device " + std::to_string(dev) + " is not sm_100 (B200); this library has no other code path");
+    out->device = dev; out->sm_count = sms;
+    return MC_OK;
+}
+
+int init_devices(const int *ids, int n) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    int visible = 0;
+    cudaError_t e = cudaGetDeviceCount(&visible);
+    if (e != cudaSuccess || visible == 0) { cudaGetLastError(); return fail(MC_ERR_NO_DEVICE, "no CUDA device visible; libmcpoker has no CPU fallback"); }
+    std::vector<int> want;
+    if (ids) want.assign(ids, ids + n);
+    else { if (n <= 0 || n > visible) n = visible; for (int i = 0; i < n; i++) want.push_back(i); }
+    for (int d : want) if (d < 0 || d >= visible) return fail(MC_ERR_INVALID, "device id out of range");
+    g_ctx.clear();
+    for (int d : want) {
+        std::unique_ptr<DevCtx> c(new DevCtx());
+        int rc = make_info(d, &c->info);
+        if (rc) return rc;
+        CU(cudaSetDevice(d));
+        c->device = d;
+        CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        CU(cudaMalloc(&c->d_small, SMALL_WORDS * sizeof(unsigned long long)));
+        CU(cudaHostAlloc(&c->h_small, SMALL_WORDS * sizeof(unsigned long long), cudaHostAllocDefault));
+        g_ctx.push_back(std::move(c));
+    }
+    return MC_OK;
+}
+
+int need_init() {
+    if (g_ctx.empty()) return fail(MC_ERR_NOT_INIT, "mc_init has not been called");
+    return MC_OK;
+}
+
+// context of the calling thread's current device (for the *_dev entry points)
+int current_info(DeviceInfo *out) {
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    for (auto &c : g_ctx) if (c->device == dev) { *out = c->info; return MC_OK; }
+    return make_info(dev, out);
+}
+
+int ensure_slots(DevCtx &c) {
+    if (c.d_in[0]) return MC_OK;
+    for (int i = 0; i < N_SLOTS; i++) {
+        CU(cudaStreamCreateWithFlags(&c.slot_stream[i], cudaStreamNonBlocking));
+        CU(cudaMalloc(&c.d_in[i], SLOT_HANDS * sizeof(uint64_t)));
+        CU(cudaMalloc(&c.d_out[i], SLOT_HANDS * sizeof(uint32_t)));
+    }
+    return MC_OK;
+}
+
+int check_equity_args(const uint64_t *hole_masks, int n_seats, uint64_t board, uint64_t dead, bool allow_random,
+                      EquityArgs *out, int *need_cards) {
+    if (!hole_masks) return fail(MC_ERR_INVALID, "hole_masks is null");
+    if (n_seats < 1 || n_seats > MC_MAX_SEATS) return fail(MC_ERR_INVALID, "n_seats must be 1..9");
+    if ((board & ~DECK_MASK) || (dead & ~DECK_MASK)) return fail(MC_ERR_INVALID, "board/dead mask has a bit that is not one of the 52 cards");
+    if (board & dead) return fail(MC_ERR_INVALID, "board and dead overlap");
+    const int nb = __builtin_popcountll(board);
+    if (nb > 5) return fail(MC_ERR_INVALID, "more than 5 community cards");
+    uint64_t used = board | dead;
+    int need = 5 - nb;
+    std::memset(out, 0, sizeof *out);
+    for (int s = 0; s < n_seats; s++) {
+        const uint64_t h = hole_masks[s];
+        if (h == 0) {
+            if (!allow_random) return fail(MC_ERR_INVALID, "a seat has no hole cards");
+            need += 2;
+        } else {
+            if ((h & ~DECK_MASK) || __builtin_popcountll(h) != 2) return fail(MC_ERR_INVALID, "a hole mask must hold exactly two of the 52 cards");
+            if (h & used) return fail(MC_ERR_INVALID, "a card is used twice");
+            used |= h;
+        }
+        out->hole[s] = h;
+    }
+    if (52 - __builtin_popcountll(used) < need) return fail(MC_ERR_INVALID, "not enough live cards");
+    out->board = board; out->dead = dead; out->n_seats = n_seats;
+    if (need_cards) *need_cards = need;
+    return MC_OK;
+}
+
+// run fn(ctx, lo, hi) on every device over an even split of [0, total), then sum `words` u64 of d_small
+template <typename F>
+int sharded_small_job(uint64_t total, int words, unsigned long long *sum, F launch) {
+    int rc = need_init();
+    if (rc) return rc;
+    const int nd = (int)g_ctx.size();
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    const uint64_t per = (total + nd - 1) / nd;
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        const uint64_t lo = std::min<uint64_t>(total, per * d), hi = std::min<uint64_t>(total, lo + per);
+        CU(cudaSetDevice(c.device));
+        CU(cudaMemsetAsync(c.d_small, 0, SMALL_WORDS * sizeof(unsigned long long), c.stream));
+        if (hi > lo) { rc = launch(c, lo, hi - lo); if (rc) return rc; }
+        CU(cudaMemcpyAsync(c.h_small, c.d_small, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    }
+    for (int i = 0; i < words; i++) sum[i] = 0;
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        CU(cudaSetDevice(c.device));
+        CU(cudaStreamSynchronize(c.stream));
+        for (int i = 0; i < words; i++) sum[i] += c.h_small[i];
+    }
+    return MC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mc_abi_version(void) { return 1; }
+const char *mc_last_error(void) { return g_err.c_str(); }
+
+int mc_init(int n_gpus, unsigned /*flags*/) { return init_devices(nullptr, n_gpus); }
+int mc_init_devices(const int *device_ids, int n) {
+    if (!device_ids || n <= 0) return fail(MC_ERR_INVALID, "device_ids is empty");
+    return init_devices(device_ids, n);
+}
+void mc_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_ctx.clear();
+}
+int mc_device_count(void) { return (int)g_ctx.size(); }
+
+uint64_t mc_card_bit(int card_id) {
+    if (card_id < 0 || card_id >= 52) return 0;
+    return 1ull << (16 * (card_id / 13) + card_id % 13 + 2);
+}
+uint32_t mc_key_packed_to_nibble(uint32_t k) { return k == MC_KEY_INVALID ? k : packed_to_nibble(k); }
+int mc_key_decode(uint32_t key, int32_t *cat, int32_t hit[5], int32_t *n_hit, int32_t kick[5], int32_t *n_kick) {
+    static const int HIT_LEN[9] = {5, 2, 4, 3, 5, 5, 5, 4, 5};     // SURVEY 7 / hand_evaluator.clj:100-133
+    const int c = (int)(key >> 20);
+    if (key == MC_KEY_INVALID || c > 8) return fail(MC_ERR_INVALID, "not a hand key");
+    int nh = 0, nk = 0;
+    for (int i = 0; i < 5; i++) {
+        const int r = (int)((key >> (16 - 4 * i)) & 15u);
+        if (i < HIT_LEN[c]) hit[nh++] = r; else kick[nk++] = r;
+    }
+    *cat = c; *n_hit = nh; *n_kick = nk;
+    return MC_OK;
+}
+
+// ---- K1 --------------------------------------------------------------------------------------------
+int mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream) {
+    if (n && (!d_masks || !d_keys)) return fail(MC_ERR_INVALID, "null device buffer");
+    DeviceInfo di;
+    int rc = current_info(&di);
+    if (rc) return rc;
+    const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
+    CU(launch_eval7_stream(d_masks, n, d_keys, mode, di, (cudaStream_t)stream));
+    return MC_OK;
+}
+int mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void *stream) {
+    return mc_eval7_batch_dev_fmt(d_masks, n, d_keys, MC_KEY_NIBBLE, stream);
+}
+
+int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_format) {
+    int rc = need_init();
+    if (rc) return rc;
+    if (n == 0) return MC_OK;
+    if (!masks || !keys) return fail(MC_ERR_INVALID, "null buffer");
+    const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
+    const int nd = (int)g_ctx.size();
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    // contiguous slice per device, each streamed through N_SLOTS staging buffers on their own streams so the
+    // H2D copy of stage i+1, the kernel of stage i and the D2H copy of stage i-1 overlap
+    const size_t per_dev = (n + nd - 1) / nd;
+    std::vector<size_t> pos(nd), end(nd);
+    for (int d = 0; d < nd; d++) {
+        pos[d] = std::min(n, per_dev * d); end[d] = std::min(n, pos[d] + per_dev);
+        if (end[d] > pos[d]) { CU(cudaSetDevice(g_ctx[d]->device)); rc = ensure_slots(*g_ctx[d]); if (rc) return rc; }
+    }
+    bool more = true;
+    for (size_t round = 0; more; round++) {
+        more = false;
+        for (int d = 0; d < nd; d++) {
+            if (pos[d] >= end[d]) continue;
+            DevCtx &c = *g_ctx[d];
+            const int s = (int)(round % N_SLOTS);
+            const size_t cnt = std::min(SLOT_HANDS, end[d] - pos[d]);
+            CU(cudaSetDevice(c.device));
+            CU(cudaMemcpyAsync(c.d_in[s], masks + pos[d], cnt * sizeof(uint64_t), cudaMemcpyHostToDevice, c.slot_stream[s]));
+            CU(launch_eval7_stream(c.d_in[s], cnt, c.d_out[s], mode, c.info, c.slot_stream[s]));
+            CU(cudaMemcpyAsync(keys + pos[d], c.d_out[s], cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.slot_stream[s]));
+            pos[d] += cnt;
+            if (pos[d] < end[d]) more = true;
+        }
+    }
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        if (!c.d_in[0]) continue;
+        CU(cudaSetDevice(c.device));
+        for (int s = 0; s < N_SLOTS; s++) CU(cudaStreamSynchronize(c.slot_stream[s]));
+    }
+    return MC_OK;
+}
+int mc_eval7_batch(const uint64_t *masks, size_t n, uint32_t *keys) {
+    return mc_eval7_batch_fmt(masks, n, keys, MC_KEY_NIBBLE);
+}
+
+int mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards, uint32_t *key) {
+    int rc = need_init();
+    if (rc) return rc;
+    if (!suit_id || !rank || !key) return fail(MC_ERR_INVALID, "null argument");
+    if (n_cards < 5) return fail(MC_ERR_TOO_FEW, "fewer than 5 cards: the reference raises ArityException here (hand_evaluator.clj:171-172)");
+    if (n_cards > 7) return fail(MC_ERR_INVALID, "more than 7 cards");
+    uint64_t m = 0;
+    for (int i = 0; i < n_cards; i++) {
+        if (suit_id[i] < 0 || suit_id[i] > 3) return fail(MC_ERR_INVALID, "suit id must be 0..3");
+        if (rank[i] < 1 || rank[i] > 14) return fail(MC_ERR_INVALID, "rank must be 1..14");
+        const uint64_t b = 1ull << (16 * suit_id[i] + rank[i]);
+        if (m & b) return fail(MC_ERR_INVALID, "duplicate card");
+        m |= b;
+    }
+    DevCtx &c = *g_ctx[0];
+    std::lock_guard<std::mutex> lk(c.mu);
+    CU(cudaSetDevice(c.device));
+    c.h_small[0] = m;
+    CU(cudaMemcpyAsync(c.d_small, c.h_small, 8, cudaMemcpyHostToDevice, c.stream));
+    CU(launch_eval7_stream(reinterpret_cast<const uint64_t *>(c.d_small), 1, reinterpret_cast<uint32_t *>(c.d_small + 2), K1_NIBBLE_FLO, c.info, c.stream));
+    CU(cudaMemcpyAsync(c.h_small + 2, c.d_small + 2, 8, cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    *key = (uint32_t)c.h_small[2];
+    return MC_OK;
+}
+
+int mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
+                       uint32_t *keys, int32_t *group_of, int32_t *n_groups) {
+    int rc = need_init();
+    if (rc) return rc;
+    EquityArgs a;
+    rc = check_equity_args(hole_masks, n_seats, board_mask, 0, false, &a, nullptr);
+    if (rc) return rc;
+    if (__builtin_popcountll(board_mask) < 3) return fail(MC_ERR_TOO_FEW, "fewer than 5 cards per player: the reference raises ArityException here");
+    DevCtx &c = *g_ctx[0];
+    std::lock_guard<std::mutex> lk(c.mu);
+    CU(cudaSetDevice(c.device));
+    uint32_t *d_out = reinterpret_cast<uint32_t *>(c.d_small);
+    CU(launch_showdown(a, d_out, c.stream));
+    CU(cudaMemcpyAsync(c.h_small, c.d_small, 20 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    const uint32_t *h = reinterpret_cast<const uint32_t *>(c.h_small);
+    for (int s = 0; s < n_seats; s++) { if (keys) keys[s] = h[s]; if (group_of) group_of[s] = (int32_t)h[10 + s]; }
+    if (n_groups) *n_groups = (int32_t)h[19];
+    return (int)h[9];       // winner bitmask (>= 0: at most 9 bits)
+}
+int mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, uint32_t *keys, uint32_t *winner_bitmask) {
+    const int rc = mc_showdown_groups(board_mask, hole_masks, n_seats, keys, nullptr, nullptr);
+    if (rc < 0) return rc;
+    if (winner_bitmask) *winner_bitmask = (uint32_t)rc;
+    return MC_OK;
+}
+
+// ---- synthetic hands ------------------------------------------------------------------------------
+int mc_random_hands_dev(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks, void *stream) {
+    if (n_cards < 1 || n_cards > 7) return fail(MC_ERR_INVALID, "n_cards must be 1..7");
+    if (n && !d_masks) return fail(MC_ERR_INVALID, "null device buffer");
+    DeviceInfo di;
+    int rc = current_info(&di);
+    if (rc) return rc;
+    CU(launch_random_hands(seed, first, n, n_cards, d_masks, di, (cudaStream_t)stream));
+    return MC_OK;
+}
+int mc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *masks) {
+    int rc = need_init();
+    if (rc) return rc;
+    if (n_cards < 1 || n_cards > 7) return fail(MC_ERR_INVALID, "n_cards must be 1..7");
+    if (n && !masks) return fail(MC_ERR_INVALID, "null buffer");
+    DevCtx &c = *g_ctx[0];
+    std::lock_guard<std::mutex> lk(c.mu);
+    CU(cudaSetDevice(c.device));
+    rc = ensure_slots(c);
+    if (rc) return rc;
+    for (size_t pos = 0; pos < n; pos += SLOT_HANDS) {
+        const size_t cnt = std::min(SLOT_HANDS, n - pos);
+        CU(launch_random_hands(seed, first + pos, cnt, n_cards, c.d_in[0], c.info, c.slot_stream[0]));
+        CU(cudaMemcpyAsync(masks + pos, c.d_in[0], cnt * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.slot_stream[0]));
+        CU(cudaStreamSynchronize(c.slot_stream[0]));
+    }
+    return MC_OK;
+}
+
+// ---- K2 ---------------------------------------------------------------------------------------------
+int mc_enumerate7_dev(uint64_t first, uint64_t count, uint64_t *d_out, void *stream) {
+    const uint64_t total = host_binom(52, 7);
+    if (first > total || count > total - first) return fail(MC_ERR_INVALID, "combination range out of bounds");
+    if (!d_out) return fail(MC_ERR_INVALID, "null device buffer");
+    DeviceInfo di;
+    int rc = current_info(&di);
+    if (rc) return rc;
+    CU(launch_enum7(first, count, reinterpret_cast<unsigned long long *>(d_out), false, di, (cudaStream_t)stream));
+    return MC_OK;
+}
+int mc_enumerate7_range(uint64_t first, uint64_t count, uint64_t hist[9], uint64_t *key_sum) {
+    const uint64_t total = host_binom(52, 7);
+    if (first > total || count > total - first) return fail(MC_ERR_INVALID, "combination range out of bounds");
+    if (!hist) return fail(MC_ERR_INVALID, "hist is null");
+    unsigned long long sum[11];
+    const bool nib = key_sum != nullptr;
+    int rc = sharded_small_job(count, 11, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        CU(launch_enum7(first + lo, cnt, c.d_small, nib, c.info, c.stream));
+        return MC_OK;
+    });
+    if (rc) return rc;
+    for (int i = 0; i < 9; i++) hist[i] = sum[i];
+    if (key_sum) *key_sum = sum[9];
+    return MC_OK;
+}
+int mc_enumerate7(uint64_t hist[9], uint64_t *key_sum) { return mc_enumerate7_range(0, host_binom(52, 7), hist, key_sum); }
+
+// ---- K3 ---------------------------------------------------------------------------------------------
+static uint64_t board_count(const EquityArgs &a) {
+    uint64_t used = a.board | a.dead;
+    for (int s = 0; s < a.n_seats; s++) used |= a.hole[s];
+    return host_binom(52 - __builtin_popcountll(used), 5 - __builtin_popcountll(a.board));
+}
+int mc_equity_exhaustive_dev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                             uint64_t first_board, uint64_t n_boards_in, int64_t *d_counts, void *stream) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, false, &a, nullptr);
+    if (rc) return rc;
+    const uint64_t total = board_count(a);
+    if (first_board > total || n_boards_in > total - first_board) return fail(MC_ERR_INVALID, "board range out of bounds");
+    if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
+    DeviceInfo di;
+    rc = current_info(&di);
+    if (rc) return rc;
+    CU(launch_equity_exhaustive(a, first_board, n_boards_in, reinterpret_cast<long long *>(d_counts), di, (cudaStream_t)stream));
+    return MC_OK;
+}
+int mc_equity_exhaustive_range(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                               uint64_t first_board, uint64_t n_boards_in, int64_t *win, int64_t *tie, int64_t *loss) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, false, &a, nullptr);
+    if (rc) return rc;
+    const uint64_t total = board_count(a);
+    if (first_board > total || n_boards_in > total - first_board) return fail(MC_ERR_INVALID, "board range out of bounds");
+    unsigned long long sum[27];
+    rc = sharded_small_job(n_boards_in, 27, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        CU(launch_equity_exhaustive(a, first_board + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.info, c.stream));
+        return MC_OK;
+    });
+    if (rc) return rc;
+    for (int s = 0; s < n_seats; s++) {
+        if (win) win[s] = (int64_t)sum[s];
+        if (tie) tie[s] = (int64_t)sum[9 + s];
+        if (loss) loss[s] = (int64_t)sum[18 + s];
+    }
+    return MC_OK;
+}
+int mc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                         int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_boards) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, false, &a, nullptr);
+    if (rc) return rc;
+    const uint64_t total = board_count(a);
+    if (n_boards) *n_boards = total;
+    return mc_equity_exhaustive_range(hole_masks, n_seats, board_mask, dead_mask, 0, total, win, tie, loss);
+}
+
+// ---- K4 ---------------------------------------------------------------------------------------------
+int mc_equity_mc_dev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                     uint64_t seed, uint64_t first_trial, uint64_t n_trials, int64_t *d_counts, void *stream) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, true, &a, nullptr);
+    if (rc) return rc;
+    if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
+    DeviceInfo di;
+    rc = current_info(&di);
+    if (rc) return rc;
+    if (n_trials) CU(launch_equity_mc(a, seed, first_trial, n_trials, reinterpret_cast<long long *>(d_counts), di, (cudaStream_t)stream));
+    return MC_OK;
+}
+int mc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                 uint64_t seed, uint64_t first_trial, uint64_t n_trials, int64_t *win, int64_t *tie, int64_t *loss) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, true, &a, nullptr);
+    if (rc) return rc;
+    unsigned long long sum[27];
+    rc = sharded_small_job(n_trials, 27, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        CU(launch_equity_mc(a, seed, first_trial + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.info, c.stream));
+        return MC_OK;
+    });
+    if (rc) return rc;
+    for (int s = 0; s < n_seats; s++) {
+        if (win) win[s] = (int64_t)sum[s];
+        if (tie) tie[s] = (int64_t)sum[9 + s];
+        if (loss) loss[s] = (int64_t)sum[18 + s];
+    }
+    return MC_OK;
+}
+
+// ---- K5 ---------------------------------------------------------------------------------------------
+namespace {
+int hole_class(uint64_t h) {                       // 169-class id of a two-card hole mask
+    const int b1 = __builtin_ctzll(h), b2 = 63 - __builtin_clzll(h);
+    const int r1 = (b1 & 15) - 2, r2 = (b2 & 15) - 2, s1 = b1 >> 4, s2 = b2 >> 4;
+    const int hi = std::max(r1, r2), lo = std::min(r1, r2);
+    if (hi == lo) return 13 * hi + hi;
+    return s1 == s2 ? 13 * hi + lo : 13 * lo + hi;
+}
+uint64_t permute_suits(uint64_t m, const int *perm) {
+    uint64_t r = 0;
+    for (int s = 0; s < 4; s++) r |= ((m >> (16 * s)) & 0xFFFFull) << (16 * perm[s]);
+    return r;
+}
+// every unordered pair of disjoint hole-card pairs, folded by the 24 suit permutations
+void build_matchups(const std::vector<std::pair<int, int>> *only_cells, std::vector<Matchup> *out) {
+    std::vector<uint64_t> holes;
+    for (int a = 0; a < 52; a++) for (int b = a + 1; b < 52; b++) holes.push_back(mc_card_bit(a) | mc_card_bit(b));
+    int perms[24][4], np = 0;
+    int p[4] = {0, 1, 2, 3};
+    do { std::memcpy(perms[np++], p, sizeof p); } while (std::next_permutation(p, p + 4));
+    std::map<std::pair<uint64_t, uint64_t>, int64_t> orbit;
+    for (size_t i = 0; i < holes.size(); i++) for (size_t j = i + 1; j < holes.size(); j++) {
+        if (holes[i] & holes[j]) continue;
+        if (only_cells) {
+            const int ca = hole_class(holes[i]), cb = hole_class(holes[j]);
+            bool hit = false;
+            for (auto &c : *only_cells) if ((c.first == ca && c.second == cb) || (c.first == cb && c.second == ca)) { hit = true; break; }
+            if (!hit) continue;
+        }
+        std::pair<uint64_t, uint64_t> best(~0ull, ~0ull);
+        for (int q = 0; q < 24; q++) {
+            uint64_t x = permute_suits(holes[i], perms[q]), y = permute_suits(holes[j], perms[q]);
+            if (x > y) std::swap(x, y);
+            best = std::min(best, std::make_pair(x, y));
+        }
+        orbit[best]++;
+    }
+    out->clear();
+    for (auto &kv : orbit) {
+        Matchup m;
+        m.hole_a = kv.first.first; m.hole_b = kv.first.second;
+        m.cell_ab = hole_class(m.hole_a) * MC_N_CLASSES + hole_class(m.hole_b);
+        m.cell_ba = hole_class(m.hole_b) * MC_N_CLASSES + hole_class(m.hole_a);
+        m.weight = kv.second;
+        out->push_back(m);
+    }
+}
+int run_matchups(const std::vector<Matchup> &mus, std::vector<long long> *wtl_full) {
+    int rc = need_init();
+    if (rc) return rc;
+    const int nd = (int)g_ctx.size();
+    const size_t cells = (size_t)MC_N_CLASSES * MC_N_CLASSES * 3;
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    // every matchup costs the same (C(48,5) boards), so a round-robin deal is already balanced
+    std::vector<std::vector<Matchup>> part(nd);
+    for (size_t i = 0; i < mus.size(); i++) part[i % nd].push_back(mus[i]);
+    std::vector<std::vector<long long>> host(nd, std::vector<long long>(cells));
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        CU(cudaSetDevice(c.device));
+        if (!c.d_wtl) CU(cudaMalloc(&c.d_wtl, cells * sizeof(long long)));
+        if (c.matchup_cap < part[d].size()) {
+            if (c.d_matchups) cudaFree(c.d_matchups);
+            CU(cudaMalloc(&c.d_matchups, part[d].size() * sizeof(Matchup)));
+            c.matchup_cap = part[d].size();
+        }
+        CU(cudaMemsetAsync(c.d_wtl, 0, cells * sizeof(long long), c.stream));
+        if (!part[d].empty()) {
+            CU(cudaMemcpyAsync(c.d_matchups, part[d].data(), part[d].size() * sizeof(Matchup), cudaMemcpyHostToDevice, c.stream));
+            CU(launch_preflop(c.d_matchups, (int)part[d].size(), c.d_wtl, c.info, c.stream));
+        }
+        CU(cudaMemcpyAsync(host[d].data(), c.d_wtl, cells * sizeof(long long), cudaMemcpyDeviceToHost, c.stream));
+    }
+    wtl_full->assign(cells, 0);
+    for (int d = 0; d < nd; d++) {
+        CU(cudaSetDevice(g_ctx[d]->device));
+        CU(cudaStreamSynchronize(g_ctx[d]->stream));
+        for (size_t i = 0; i < cells; i++) (*wtl_full)[i] += host[d][i];
+    }
+    return MC_OK;
+}
+}  // namespace
+
+int mc_preflop_matrix(int64_t *wtl) {
+    if (!wtl) return fail(MC_ERR_INVALID, "wtl is null");
+    std::vector<Matchup> mus;
+    build_matchups(nullptr, &mus);
+    std::vector<long long> full;
+    int rc = run_matchups(mus, &full);
+    if (rc) return rc;
+    for (size_t i = 0; i < full.size(); i++) wtl[i] = full[i];
+    return MC_OK;
+}
+int mc_preflop_cells(const int32_t *class_a, const int32_t *class_b, int n_cells, int64_t *wtl) {
+    if (!class_a || !class_b || !wtl || n_cells <= 0) return fail(MC_ERR_INVALID, "bad cell list");
+    std::vector<std::pair<int, int>> cells;
+    for (int i = 0; i < n_cells; i++) {
+        if (class_a[i] < 0 || class_a[i] >= MC_N_CLASSES || class_b[i] < 0 || class_b[i] >= MC_N_CLASSES) return fail(MC_ERR_INVALID, "class id out of range");
+        cells.emplace_back(class_a[i], class_b[i]);
+    }
+    std::vector<Matchup> mus;
+    build_matchups(&cells, &mus);
+    std::vector<long long> full;
+    int rc = run_matchups(mus, &full);
+    if (rc) return rc;
+    for (int i = 0; i < n_cells; i++)
+        for (int k = 0; k < 3; k++) wtl[3 * i + k] = full[((size_t)class_a[i] * MC_N_CLASSES + class_b[i]) * 3 + k];
+    return MC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,50 @@
+// kernels.cuh -- launch wrappers of the sm_100a kernels (kernels.cu), called by the C ABI (capi.cu).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mcp {
+
+constexpr int MAX_SEATS = 9;
+
+// K1 variants (DESIGN.md "K1"): how the public nibble key is produced
+enum K1Mode : int {
+    K1_PACKED = 0,        // packed key, no conversion
+    K1_NIBBLE_TABLE = 1,  // nibble key through the shared-memory rank-set table (default)
+    K1_NIBBLE_FLO = 2,    // nibble key through FLO/clz loops, no table (A/B variant)
+};
+
+struct DeviceInfo { int sm_count; int device; };
+
+cudaError_t launch_eval7_stream(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int mode,
+                                const DeviceInfo &di, cudaStream_t st);
+cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,
+                                const DeviceInfo &di, cudaStream_t st);
+// out: 11 x u64 = hist[9], sum of nibble keys (0 unless nib_sum), sum of packed keys; accumulated into
+cudaError_t launch_enum7(uint64_t first, uint64_t count, unsigned long long *d_out, bool nib_sum,
+                         const DeviceInfo &di, cudaStream_t st);
+
+struct EquityArgs {
+    uint64_t hole[MAX_SEATS];   // 0 = random seat (Monte Carlo only)
+    uint64_t board;             // known community cards
+    uint64_t dead;
+    int n_seats;
+};
+// d_counts: 27 x int64 = win[9] tie[9] loss[9]; accumulated into
+cudaError_t launch_equity_exhaustive(const EquityArgs &a, uint64_t first_board, uint64_t n_boards,
+                                     long long *d_counts, const DeviceInfo &di, cudaStream_t st);
+cudaError_t launch_equity_mc(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                             long long *d_counts, const DeviceInfo &di, cudaStream_t st);
+// one warp: keys per seat, winner bitmask, tie-group index per seat, number of groups
+// d_out: uint32 keys[9], uint32 winners, int32 group_of[9], int32 n_groups  (20 words)
+cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, cudaStream_t st);
+
+// preflop matrix: matchup list = (hole_a, hole_b, cell index, weight); each block takes matchups
+struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weight; };
+cudaError_t launch_preflop(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
+                           const DeviceInfo &di, cudaStream_t st);
+
+uint64_t host_binom(int n, int k);
+
+}  // namespace mcp

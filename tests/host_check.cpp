@@ -1,0 +1,45 @@
+// host_check.cpp -- TEST HARNESS: compiles the product's evaluator header (plain integer code) with g++ and
+// checks it against the CPU oracle, so the formulation can be verified exhaustively on a box without a GPU.
+// Not part of the product; the product calls these functions from CUDA kernels only.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "../monte-carlo_b200/csrc/eval.cuh"
+#include "../oracle/mc_oracle.h"
+
+static uint64_t BINOM[65][9];
+static void unrank(uint64_t idx, int k, int *c) {
+    for (int i = k; i >= 1; i--) { int x = i - 1; while (BINOM[x + 1][i] <= idx) x++; c[i - 1] = x; idx -= BINOM[x][i]; }
+}
+static int next(int *c, int k, int n) {
+    for (int i = 0; i < k; i++) { int lim = (i + 1 < k) ? c[i + 1] : n; if (c[i] + 1 < lim) { c[i]++; for (int j = 0; j < i; j++) c[j] = j; return 1; } }
+    return 0;
+}
+int main(int argc, char **argv) {
+    int use56 = argc > 1 ? atoi(argv[1]) : 0;     // 1: 56-card deck incl. rank 1 (k = 5 only)
+    for (int n = 0; n <= 64; n++) for (int k = 0; k <= 8; k++) BINOM[n][k] = k == 0 ? 1 : (n == 0 ? 0 : BINOM[n - 1][k - 1] + BINOM[n - 1][k]);
+    int ncards = use56 ? 56 : 52, per = use56 ? 14 : 13, base = use56 ? 1 : 2;
+    uint64_t bad = 0, total_all = 0;
+    for (int k = 5; k <= (use56 ? 6 : 7); k++) {
+        uint64_t total = BINOM[ncards][k];
+        uint64_t kbad = 0;
+#pragma omp parallel for reduction(+ : kbad) schedule(static, 1)
+        for (int t = 0; t < 64; t++) {
+            uint64_t chunk = (total + 63) / 64, lo = chunk * t, hi = lo + chunk > total ? total : lo + chunk;
+            if (lo >= hi) continue;
+            int c[7]; unrank(lo, k, c);
+            for (uint64_t i = lo; i < hi; i++) {
+                uint64_t m = 0;
+                for (int j = 0; j < k; j++) m |= 1ull << (16 * (c[j] / per) + c[j] % per + base);
+                uint32_t want = orc_eval_mask(m);
+                uint32_t pk = mcp::eval_packed(m);
+                uint32_t got = mcp::packed_to_nibble(pk);
+                if (got != want || !mcp::valid_hand(m)) { if (kbad < 5) fprintf(stderr, "MISMATCH k=%d mask=%016llx want=%06x got=%06x packed=%08x\n", k, (unsigned long long)m, want, got, pk); kbad++; }
+                next(c, k, ncards);
+            }
+        }
+        printf("k=%d deck=%d hands=%llu mismatches=%llu\n", k, ncards, (unsigned long long)total, (unsigned long long)kbad);
+        bad += kbad; total_all += total;
+    }
+    return bad ? 1 : 0;
+}
