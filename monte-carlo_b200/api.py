@@ -1,0 +1,134 @@
+"""numpy-facing wrappers over the C ABI (host buffers in, host buffers out).  These are what the Python
+mirror of the reference's namespaces (hand_evaluator.py, gameplay.py), the tests and bench.py's end-to-end
+leg call; each is a thin argument-marshalling layer over one mc_* entry point."""
+import ctypes as C
+
+import numpy as np
+
+from . import engine as E
+
+HIT_LEN = (5, 2, 4, 3, 5, 5, 5, 4, 5)        # per category 0..8 (hand_evaluator.clj:100-133)
+
+
+def card_bit(card_id):
+    return int(E.lib().mc_card_bit(int(card_id)))
+
+
+def mask_of_ids(ids):
+    m = 0
+    for i in ids:
+        b = card_bit(i)
+        if not b:
+            raise ValueError("card id out of range: %r" % (i,))
+        m |= b
+    return m
+
+
+def key_decode(key):
+    """nibble key -> [cat, [hit...], [kick...]] exactly as the Clojure value (cat 6 slot 1 as a vector)."""
+    cat, nh, nk = C.c_int32(), C.c_int32(), C.c_int32()
+    hit, kick = (C.c_int32 * 5)(), (C.c_int32 * 5)()
+    E.check(E.lib().mc_key_decode(int(key), C.byref(cat), hit, C.byref(nh), kick, C.byref(nk)))
+    return [cat.value, list(hit[:nh.value]), list(kick[:nk.value])]
+
+
+def key_packed_to_nibble(key):
+    return int(E.lib().mc_key_packed_to_nibble(int(key)))
+
+
+def eval_cards(suit_ids, ranks):
+    E.ensure_init()
+    n = len(ranks)
+    s = (C.c_int32 * max(n, 1))(*suit_ids)
+    r = (C.c_int32 * max(n, 1))(*ranks)
+    key = C.c_uint32(0)
+    E.check(E.lib().mc_eval_cards(s, r, n, C.byref(key)))
+    return key.value
+
+
+def eval7_batch(masks, key_format=E.KEY_NIBBLE, out=None):
+    E.ensure_init()
+    masks = np.ascontiguousarray(masks, dtype=np.uint64)
+    keys = out if out is not None else np.empty(masks.shape[0], dtype=np.uint32)
+    E.check(E.lib().mc_eval7_batch_fmt(masks.ctypes.data, masks.shape[0], keys.ctypes.data, key_format))
+    return keys
+
+
+def random_hands(seed, first, n, n_cards=7):
+    E.ensure_init()
+    out = np.empty(n, dtype=np.uint64)
+    E.check(E.lib().mc_random_hands(seed, first, n, n_cards, out.ctypes.data))
+    return out
+
+
+def showdown(board_mask, hole_masks):
+    """-> (keys per seat, winner bitmask, tie-group index per seat (0 = best), number of groups)"""
+    E.ensure_init()
+    n = len(hole_masks)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    keys, groups, ng = (C.c_uint32 * 9)(), (C.c_int32 * 9)(), C.c_int32(0)
+    rc = E.check(E.lib().mc_showdown_groups(board_mask, h, n, keys, groups, C.byref(ng)))
+    return list(keys[:n]), rc, list(groups[:n]), ng.value
+
+
+def enumerate7(first=None, count=None, key_sum=True):
+    E.ensure_init()
+    hist, ks = (C.c_uint64 * 9)(), C.c_uint64(0)
+    ksp = C.byref(ks) if key_sum else None
+    if first is None:
+        E.check(E.lib().mc_enumerate7(hist, ksp))
+    else:
+        E.check(E.lib().mc_enumerate7_range(first, count, hist, ksp))
+    return list(hist), (ks.value if key_sum else None)
+
+
+def _seat_arrays(n):
+    return (C.c_int64 * 9)(), (C.c_int64 * 9)(), (C.c_int64 * 9)()
+
+
+def equity_exhaustive(hole_masks, board_mask=0, dead_mask=0, first=None, count=None):
+    E.ensure_init()
+    n = len(hole_masks)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    w, t, l = _seat_arrays(n)
+    nb = C.c_uint64(0)
+    if first is None:
+        E.check(E.lib().mc_equity_exhaustive(h, n, board_mask, dead_mask, w, t, l, C.byref(nb)))
+    else:
+        E.check(E.lib().mc_equity_exhaustive_range(h, n, board_mask, dead_mask, first, count, w, t, l))
+        nb.value = count
+    return list(w[:n]), list(t[:n]), list(l[:n]), nb.value
+
+
+def equity_mc(hole_masks, board_mask, dead_mask, seed, first_trial, n_trials):
+    E.ensure_init()
+    n = len(hole_masks)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    w, t, l = _seat_arrays(n)
+    E.check(E.lib().mc_equity_mc(h, n, board_mask, dead_mask, seed, first_trial, n_trials, w, t, l))
+    return list(w[:n]), list(t[:n]), list(l[:n])
+
+
+def preflop_cells(cells):
+    E.ensure_init()
+    n = len(cells)
+    a = (C.c_int32 * n)(*[c[0] for c in cells])
+    b = (C.c_int32 * n)(*[c[1] for c in cells])
+    out = np.zeros((n, 3), dtype=np.int64)
+    E.check(E.lib().mc_preflop_cells(a, b, n, out.ctypes.data))
+    return out
+
+
+def preflop_matrix():
+    E.ensure_init()
+    out = np.zeros((E.N_CLASSES, E.N_CLASSES, 3), dtype=np.int64)
+    E.check(E.lib().mc_preflop_matrix(out.ctypes.data))
+    return out
+
+
+def hole_class(rank_a, rank_b, suited):
+    """169-class id: x = rank-2; pair 13x+x; suited 13*hi+lo; offsuit 13*lo+hi"""
+    hi, lo = max(rank_a, rank_b) - 2, min(rank_a, rank_b) - 2
+    if hi == lo:
+        return 13 * hi + hi
+    return 13 * hi + lo if suited else 13 * lo + hi

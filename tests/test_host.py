@@ -1,0 +1,122 @@
+"""CPU-only: host-side logic, the C-ABI library's exports, and the product evaluator's formulation compiled
+for the host (tests/host_check.cpp) against the oracle on every 5-, 6- and 7-card hand."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+Card = None
+
+
+def test_library_loads_and_exports_every_declared_symbol(pkg):
+    L = pkg.engine.lib()
+    header = open(os.path.join(ROOT, "include", "mcpoker.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(mc_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    assert declared == set(pkg.engine.EXPORTS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.mc_abi_version() == 1
+
+
+def test_no_gpu_means_loud_failure_not_fallback(pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.engine.McError) as e:
+        pkg.engine.init()
+    assert e.value.code == pkg.engine.MC_ERR_NO_DEVICE
+    with pytest.raises(pkg.engine.McError) as e:
+        pkg.engine.check(pkg.engine.lib().mc_enumerate7((C.c_uint64 * 9)(), None))
+    assert e.value.code == pkg.engine.MC_ERR_NOT_INIT
+
+
+def test_pure_helpers(pkg, oracle):
+    api = pkg.api
+    assert [api.card_bit(i) for i in (0, 12, 13, 51)] == [oracle.card_bit(i) for i in (0, 12, 13, 51)]
+    assert api.card_bit(52) == 0
+    assert api.key_decode(0x8_98765) == [8, [9, 8, 7, 6, 5], []]
+    assert api.key_decode(0x7_11113) == [7, [1, 1, 1, 1], [3]]
+    assert api.key_decode(0x6_88899) == [6, [8, 8, 8, 9, 9], []]
+    assert api.key_decode(0x3_55582) == [3, [5, 5, 5], [8, 2]]
+    assert api.key_decode(0x2_55228) == [2, [5, 5, 2, 2], [8]]
+    assert api.key_decode(0x1_55876) == [1, [5, 5], [8, 7, 6]]
+    assert api.key_decode(0x0_87642) == [0, [8, 7, 6, 4, 2], []]
+    with pytest.raises(pkg.engine.McError):
+        api.key_decode(0xFFFFFFFF)
+    # packed <-> nibble: cat 1, pair of 5s (bit 4), kickers 8 7 6 (bits 7,6,5)
+    packed = (1 << 28) | ((1 << 4) << 14) | (1 << 7 | 1 << 6 | 1 << 5)
+    assert api.key_packed_to_nibble(packed) == 0x155876
+    assert api.hole_class(14, 14, False) == 168 and api.hole_class(13, 13, False) == 154
+    assert api.hole_class(14, 13, True) == 13 * 12 + 11 and api.hole_class(14, 13, False) == 13 * 11 + 12
+
+
+def test_card_module_matches_card_clj(pkg):
+    card = pkg.card
+    assert len(card.COMPLETE_DECK) == 52
+    assert card.COMPLETE_DECK[0] == card.Card("hearts", 2) and card.COMPLETE_DECK[51] == card.Card("clubs", 14)
+    assert [card.card_id(c) for c in card.COMPLETE_DECK] == list(range(52))
+    assert card.from_wire({"suit": "hearts", "rank": 8}) == card.Card("hearts", 8)
+
+
+def test_mirror_predicates_like_the_reference_tests(pkg):
+    """hand_evaluator_test.clj:6-55 against the plain host predicates of the mirror module"""
+    import random
+    he, card = pkg.hand_evaluator, pkg.card
+    deck = list(card.COMPLETE_DECK)
+    assert he.constant_coll_p([1, 1, 1])
+    assert not he.constant_coll_p([1, 1, 2]) and not he.constant_coll_p([1, 2, 1]) and not he.constant_coll_p([2, 1, 1])
+    h1 = deck[:5]
+    random.Random(0).shuffle(h1)
+    assert he.straight_p(h1) and not he.straight_p(deck[::2][:5])
+    twos = [c for c in deck if c.rank == 2]
+    threes = [c for c in deck if c.rank == 3]
+    fours = [c for c in deck if c.rank == 4]
+    assert he.n_of_a_kind_p(twos, 4) and he.n_of_a_kind_p(twos, 3) and he.n_of_a_kind_p(twos, 2)
+    assert not he.n_of_a_kind_p(twos[:2] + threes[:2], 4) and not he.n_of_a_kind_p(twos[:2] + threes[:2], 3)
+    assert he.n_of_a_kind_p(twos[:2] + threes[:2], 2)
+    assert he.full_house_p(twos) and not he.full_house_p(twos + threes[:1])
+    assert he.full_house_p(twos[:3] + threes[:2])
+    assert not he.full_house_p(twos[:2] + threes[:1] + fours[:1])
+    assert not he.full_house_p(twos[:2] + threes[:2] + fours[:1])
+    assert he.two_pair_p(twos) and he.two_pair_p(twos + threes[:1]) and he.two_pair_p(twos[:3] + threes[:2])
+    assert not he.two_pair_p(twos[:2] + threes[:1] + fours[:1])
+    assert he.two_pair_p(twos[:2] + threes[:2] + fours[:1])
+    assert he.max_hand_value([1, [5, 5], [8, 7, 6]], [0, [8, 7, 6, 4, 2], []]) == [1, [5, 5], [8, 7, 6]]
+    assert he.max_hand_value([6, [8, 8, 8, 9, 9], []], [6, [9, 9, 9, 8, 8], []]) == [6, [9, 9, 9, 8, 8], []]
+
+
+def test_pack_resuits_repeated_cards(pkg):
+    he, card = pkg.hand_evaluator, pkg.card
+    C_ = card.Card
+    ids, ranks = he._pack([C_("h", 5), C_("d", 2), C_("s", 3), C_("c", 5), C_("h", 5)])   # test.clj:92
+    assert ranks == [5, 2, 3, 5, 5] and len(set(zip(ids, ranks))) == 5 and len(set(ids)) >= 2
+    with pytest.raises(ValueError):
+        he._pack([C_("h", 5), C_("h", 5), C_("h", 2), C_("h", 3), C_("h", 4)])
+
+
+def test_group_winners_and_update_stacks(pkg):
+    gp = pkg.gameplay
+    entries = [{"player": "a", "hand_value": [3, [5, 5, 5], [8, 2]]}, {"player": "b", "hand_value": [3, [5, 5, 5], [8, 2]]},
+               {"player": "c", "hand_value": [1, [5, 5], [8, 7, 6]]}]
+    assert gp.group_winners(entries) == [{"a", "b"}, {"c"}]
+    stacks = gp.update_stacks([{"bet": 10, "n": 3, "players": {"a", "b", "c"}}, {"bet": 5, "n": 1, "players": {"c"}}],
+                              [{"a", "b"}, {"c"}], {"a": 0, "b": 0, "c": 0})
+    assert stacks == {"a": 15, "b": 15, "c": 5}
+
+
+def test_product_evaluator_formulation_on_every_hand(oracle):
+    """eval.cuh (the product's device evaluator, plain integer code) compiled with g++ == oracle on all
+    C(52,5)+C(52,6)+C(52,7) hands and on the 56-card deck that includes the tests' rank 1."""
+    exe = "/tmp/mcp_host_check"
+    subprocess.check_call(["/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++", "-O2", "-fopenmp", "-o", exe,
+                           os.path.join(ROOT, "tests", "host_check.cpp"), "-L" + oracle.ORACLE_DIR, "-loracle",
+                           "-Wl,-rpath," + oracle.ORACLE_DIR])
+    for arg in ("0", "1"):
+        out = subprocess.run([exe, arg], capture_output=True, text=True)
+        assert out.returncode == 0, out.stdout + out.stderr
+        assert "mismatches=0" in out.stdout

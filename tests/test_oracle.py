@@ -1,0 +1,240 @@
+"""CPU-only: pins the oracle against every assert of the reference's own test file
+(/root/reference/test/montecarlo/hand_evaluator_test.clj) and cross-checks its three formulations."""
+import ctypes as C
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.json")))
+SG = GOLD["survey_goldens"]
+
+# COMPLETE-DECK of card.clj:10-13 as (suit, rank)
+DECK = [(s, r) for s in range(4) for r in range(2, 15)]
+TWOS = [c for c in DECK if c[1] == 2]
+THREES = [c for c in DECK if c[1] == 3]
+FOURS = [c for c in DECK if c[1] == 4]
+
+
+def test_constant_coll(oracle):                 # hand_evaluator_test.clj:6-11
+    f = lambda xs: oracle.lib().orc_constant_coll((C.c_int * len(xs))(*xs), len(xs))
+    assert f([1, 1, 1])
+    assert not f([1, 1, 2])
+    assert not f([1, 2, 1])
+    assert not f([2, 1, 1])
+
+
+def test_straight_p(oracle):                    # :13-18
+    h1 = DECK[:5][:]
+    random.Random(1).shuffle(h1)
+    h2 = DECK[::2][:5]
+    assert oracle.lib().orc_straight_p(oracle.cards(h1), 5)
+    assert not oracle.lib().orc_straight_p(oracle.cards(h2), 5)
+
+
+def test_n_of_a_kind_p(oracle):                 # :20-29
+    f = lambda cs, n: oracle.lib().orc_n_of_a_kind_p(oracle.cards(cs), len(cs), n, None)
+    assert f(TWOS, 4) and f(TWOS, 3) and f(TWOS, 2)
+    mix = TWOS[:2] + THREES[:2]
+    assert not f(mix, 4)
+    assert not f(mix, 3)
+    random.Random(2).shuffle(mix)
+    assert f(mix, 2)
+
+
+def test_full_house_p(oracle):                  # :31-42 (four 2s count as a "full house": SURVEY 4)
+    f = lambda cs: oracle.lib().orc_full_house_p(oracle.cards(cs), len(cs))
+    assert f(TWOS)
+    assert not f(TWOS + THREES[:1])
+    assert f(TWOS[:3] + THREES[:2])
+    assert not f(TWOS[:2] + THREES[:1] + FOURS[:1])
+    assert not f(TWOS[:2] + THREES[:2] + FOURS[:1])
+
+
+def test_two_pair_p(oracle):                    # :44-55
+    f = lambda cs: oracle.lib().orc_two_pair_p(oracle.cards(cs), len(cs))
+    assert f(TWOS)
+    assert f(TWOS + THREES[:1])
+    assert f(TWOS[:3] + THREES[:2])
+    assert not f(TWOS[:2] + THREES[:1] + FOURS[:1])
+    assert f(TWOS[:2] + THREES[:2] + FOURS[:1])
+
+
+@pytest.mark.parametrize("vec", GOLD["evaluator"], ids=lambda v: "line%d" % v["line"])
+def test_evaluator_reference_vectors(oracle, vec):      # :57-137, all 13 asserts
+    cards = [tuple(c) for c in vec["cards"]]
+    orders = [cards]
+    if vec["shuffle"]:
+        rng = random.Random(vec["line"])
+        for _ in range(20):
+            c = cards[:]
+            rng.shuffle(c)
+            orders.append(c)
+    for c in orders:
+        v = oracle.evaluator(c)
+        assert v.as_list() == vec["want"]
+        key = oracle.lib().orc_value_to_key(C.byref(v))
+        # all three formulations give the same key.  Four of the reference's vectors (:92, :99, :105, :125)
+        # hold the same card twice ((card/->Card :h 5) ... (card/->Card :h 5)), which no card SET can
+        # express: those pin the literal evaluator only (the host shim re-suits duplicates, see
+        # hand_evaluator._pack).
+        if len(set(c)) == 5:
+            assert oracle.lib().orc_eval_mask(oracle.mask_of(c)) == key
+            assert oracle.lib().orc_best_of_subsets_key(oracle.mask_of(c)) == key
+        back = oracle.Value()
+        oracle.lib().orc_key_to_value(key, C.byref(back))
+        assert back.as_list() == vec["want"]
+
+
+def test_full_house_is_lazyseq_and_compare_throws(oracle):
+    a = oracle.evaluator([(0, 9), (1, 8), (2, 9), (3, 8), (0, 8)])
+    b = oracle.evaluator([(0, 9), (1, 9), (2, 9), (3, 8), (0, 8)])
+    assert a.hit_is_lazyseq and b.hit_is_lazyseq
+    thr = C.c_int(0)
+    assert oracle.lib().orc_compare(C.byref(a), C.byref(b), C.byref(thr)) < 0 and thr.value == 1
+    c = oracle.evaluator([(0, 5), (1, 7), (2, 8), (3, 6), (0, 5)])
+    thr = C.c_int(0)
+    assert oracle.lib().orc_compare(C.byref(a), C.byref(c), C.byref(thr)) > 0 and thr.value == 0
+
+
+def test_no_wheel(oracle):
+    assert oracle.evaluator([(0, 14), (1, 2), (2, 3), (3, 4), (0, 5)]).as_list() == [0, [14, 5, 4, 3, 2], []]
+    assert oracle.evaluator([(0, 14), (0, 2), (0, 3), (0, 4), (0, 5)]).as_list() == [5, [14, 5, 4, 3, 2], []]
+
+
+def test_too_few_cards(oracle):
+    rc, _, _ = oracle.player_hand_value([(0, 2), (1, 3)])
+    assert rc == -1
+    assert oracle.lib().orc_eval_mask(oracle.mask_of([(0, 2), (1, 3)])) == 0xFFFFFFFF
+
+
+def test_literal_equals_fast_on_all_5card_hands(oracle):
+    """literal 120-permutation evaluator == rank-count evaluator == direct evaluator on all C(52,5) hands"""
+    import itertools
+    L = oracle.lib()
+    ids = np.array(list(itertools.combinations(range(52), 5)), dtype=np.int64)
+    bits = np.array([oracle.card_bit(i) for i in range(52)], dtype=np.uint64)
+    masks = np.bitwise_or.reduce(bits[ids], axis=1)
+    k_direct = oracle.eval_batch(masks, 0)
+    k_rc = oracle.eval_batch(masks, 1)
+    k_lit = oracle.eval_batch(masks, 2)
+    assert np.array_equal(k_direct, k_rc)
+    assert np.array_equal(k_direct, k_lit)
+    assert len(np.unique(k_lit)) == SG["distinct5"]
+    hist = np.bincount(k_lit >> 20, minlength=9)[::-1].tolist()
+    assert hist == SG["hist5_cat8to0"]
+    assert int(k_lit.astype(np.uint64).sum()) == SG["keysum5"]
+
+
+def test_literal_7card_sample_and_throw_flag(oracle):
+    masks = oracle.random_hands(0x5EED5EED, 0, 3000)
+    k_lit = oracle.eval_batch(masks, 2)
+    assert np.array_equal(k_lit, oracle.eval_batch(masks, 0))
+    # the reference raises for every 3-3-1 and 3-2-2 rank pattern (two full-house subsets meet in the reduce)
+    L = oracle.lib()
+    n_throw = 0
+    for m in masks[:1000]:
+        thr = C.c_int(0)
+        L.orc_eval_mask_literal(int(m), C.byref(thr))
+        counts = sorted(np.bincount([(b & 15) for b in range(64) if (int(m) >> b) & 1]).tolist(), reverse=True)
+        pattern = [c for c in counts if c]
+        if pattern in ([3, 3, 1], [3, 2, 2]):
+            assert thr.value == 1
+        if pattern[0] < 3 or (pattern[0] == 3 and pattern[1] < 2):
+            assert thr.value == 0
+        n_throw += thr.value
+    assert n_throw > 0
+
+
+def test_enumeration_goldens_6_and_7(oracle):
+    h6, _, _ = oracle.enumerate_hands(6, 0)
+    assert h6[::-1] == SG["hist6_cat8to0"]
+    h7, ks7, d7 = oracle.enumerate_hands(7, 0, distinct=True)
+    assert h7[::-1] == SG["hist7_cat8to0"]
+    assert ks7 == SG["keysum7"] and d7 == SG["distinct7"]
+
+
+def test_crosscheck_direct_vs_best_of_subsets_exhaustive_6(oracle):
+    assert oracle.lib().orc_enumerate_crosscheck(6, 0) == 0
+
+
+def test_crosscheck_7_card_sample_ranges(oracle):
+    # the full C(52,7) cross-check runs in oracle/selfcheck (about a minute); here: 3 ranges of 2M hands
+    L = oracle.lib()
+    for first in (0, 60_000_000, 131_784_560):
+        h0, s0, _ = oracle.enumerate_hands(7, 0, first=first, count=2_000_000)
+        h1, s1, _ = oracle.enumerate_hands(7, 1, first=first, count=2_000_000)
+        assert h0 == h1 and s0 == s1
+
+
+def test_enumeration_range_split_is_additive(oracle):
+    full, ks, _ = oracle.enumerate_hands(6, 0)
+    a, ka, _ = oracle.enumerate_hands(6, 0, first=0, count=7_000_000)
+    b, kb, _ = oracle.enumerate_hands(6, 0, first=7_000_000, count=0)
+    assert [x + y for x, y in zip(a, b)] == full and ka + kb == ks
+
+
+@pytest.mark.parametrize("name", ["aa_kk_no_shared", "aa_kk_both_shared", "aa_kk_one_shared"])
+def test_equity_goldens(oracle, name):
+    g = SG[name]
+    holes = [oracle.card_bit(a) | oracle.card_bit(b) for a, b in g["holes_ids"]]
+    rc, w, t, l, nb = oracle.equity_exhaustive(holes)
+    assert rc == 0 and nb == 1712304
+    assert (w[0], w[1], t[0]) == (g["win_a"], g["win_b"], g["tie"])
+    assert l == [w[1], w[0]] and t[0] == t[1]
+
+
+def test_philox_known_answers(oracle):
+    for v in GOLD["philox_kat"]["vectors"]:
+        assert ["%08x" % x for x in oracle.philox(v["ctr"], v["key"])] == v["out"]
+
+
+def test_random_hands_are_valid_and_deterministic(oracle):
+    a = oracle.random_hands(0x5EED5EED, 0, 10000)
+    b = oracle.random_hands(0x5EED5EED, 5000, 5000)
+    assert np.array_equal(a[5000:], b)
+    assert all(bin(int(m)).count("1") == 7 for m in a[:2000])
+    assert not np.any(a & np.uint64(~0x7FFC7FFC7FFC7FFC & 0xFFFFFFFFFFFFFFFF))
+
+
+def test_mc_split_invariance_and_symmetry(oracle):
+    holes = [oracle.card_bit(12) | oracle.card_bit(25)] + [0] * 8
+    rc, w, t, l = oracle.equity_mc(holes, 0, 0, 0x5EED5EED, 0, 1 << 16)
+    assert rc == 0
+    rc, w1, t1, l1 = oracle.equity_mc(holes, 0, 0, 0x5EED5EED, 0, 30000)
+    rc, w2, t2, l2 = oracle.equity_mc(holes, 0, 0, 0x5EED5EED, 30000, (1 << 16) - 30000)
+    assert [a + b for a, b in zip(w1, w2)] == w and [a + b for a, b in zip(t1, t2)] == t
+    assert all(w[s] + t[s] + l[s] == 1 << 16 for s in range(9))
+    # AA against 8 random hands wins roughly a third of the time; the random seats are exchangeable
+    assert 0.30 < (w[0] + t[0] / 2) / (1 << 16) < 0.40
+    others = [w[s] / (1 << 16) for s in range(1, 9)]
+    assert max(others) - min(others) < 0.02
+
+
+def test_deal_order_matches_reference_deal_hand(oracle):
+    """seat i gets accepted draws i and i+n (gameplay.clj:63-75), then the community cards"""
+    L = oracle.lib()
+    holes_in = (C.c_uint64 * 3)(0, 0, 0)
+    holes_out, board = (C.c_uint64 * 3)(), C.c_uint64(0)
+    L.orc_deal_trial(holes_in, 3, 0, 0, 7, 42, holes_out, C.byref(board))
+    used = 0
+    for h in holes_out:
+        assert bin(h).count("1") == 2 and not (h & used)
+        used |= h
+    assert bin(board.value).count("1") == 5 and not (board.value & used)
+
+
+def test_group_winners(oracle):                                   # gameplay.clj:118-120,127-132
+    keys = (C.c_uint32 * 5)(0x100000, 0x300000, 0x100000, 0x300000, 0x200000)
+    g = (C.c_int * 5)()
+    assert oracle.lib().orc_group_winners(keys, 5, g) == 3
+    assert list(g) == [2, 0, 2, 0, 1]
+
+
+def test_preflop_cell_aa_kk(oracle):
+    wtl = (C.c_int64 * 3)()
+    assert oracle.lib().orc_preflop_cell(168, 154, 0, wtl) == 0
+    g = SG["cell_AA_KK"]
+    assert list(wtl) == [g["win"], g["tie"], g["loss"]]
