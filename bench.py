@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py -- headline measurement of the hand-ranking hot path (see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]           our arm (one process per GPU under torchrun)
+  python bench.py --impl reference ...                          the reference's CPU algorithm (oracle port)
+
+A step = one pass of K1 (eval7_stream) over one resident batch of 2^28 Philox-seeded 7-card hands per GPU
+(2 GiB of masks in, 1 GiB of keys out: far larger than the 126 MB L2).  `value` = total 7-card evals/s over
+all ranks with inputs resident in HBM, device-timed with CUDA events on the launching stream, max over
+ranks.  `e2e` = the same metric through the host-buffer C-ABI call mc_eval7_batch (pinned host memory,
+H2D + kernel + D2H inside the timed region).  `workloads` adds BASELINE configs 2, 3 and 4 (enumeration,
+exhaustive AA-KK, 9-seat Monte Carlo with one NCCL all-reduce of the int64 counts at N > 1).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+SEED = 0x5EED5EED
+BATCH_LOG2 = 28                  # hands per GPU per step (K1)
+E2E_LOG2 = 26                    # hands per GPU per step through the host-buffer call
+ALGO_BYTES_PER_EVAL = 12         # 8 B mask in + 4 B key out
+OPS = {"eval": 64, "enum": 70, "board2": 140, "mc9": 1024}       # declared thread-level int ops
+METRIC = "7-card evals/s"
+
+
+def load_peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), float(p.get("sm_max_mhz", 1965.0)), "measured"
+    except Exception:
+        return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler:
+    """samples nvidia-smi during the timed region (B200_PROFILING.md clocks line)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(float(r[1]) for r in self.rows if len(r) > 2 and r[1].replace(".", "").isdigit())
+        mx = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 9 for n, v in zip(names, r[5:9]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_port_baseline(oracle, seconds_target=12.0):
+    """the reference's algorithm (literal port, all host threads) on a bounded sample of the K1 workload"""
+    cores = oracle.lib().orc_max_threads()
+    probe = oracle.random_hands(SEED, 0, 4000 * cores)
+    t = time.perf_counter()
+    oracle.eval_batch(probe, 2, 0)
+    rate = len(probe) / (time.perf_counter() - t)
+    n = max(len(probe), int(rate * seconds_target))
+    masks = oracle.random_hands(SEED, 0, n)
+    t = time.perf_counter()
+    oracle.eval_batch(masks, 2, 0)
+    dt = time.perf_counter() - t
+    return n / dt, cores, n, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU algorithm for the path.  The Clojure original cannot run here
+    (no JVM on the image), so this is the literal C port in oracle/ref_literal.c, all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle_lib as oracle
+    cores = oracle.lib().orc_max_threads()
+    probe = oracle.random_hands(SEED, 0, 2000 * cores)
+    t = time.perf_counter()
+    oracle.eval_batch(probe, 2, 0)
+    rate = len(probe) / (time.perf_counter() - t)
+    budget = 120.0 / max(1, args.steps + args.warmup)            # whole run within a few minutes
+    n = max(1000, int(rate * min(10.0, budget)))
+    masks = oracle.random_hands(SEED, 0, n)
+    for _ in range(args.warmup):
+        oracle.eval_batch(masks, 2, 0)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.eval_batch(masks, 2, 0)
+    dt = time.perf_counter() - t
+    value = n * args.steps / dt
+    fast_t = time.perf_counter()
+    oracle.eval_batch(masks, 0, 0)
+    fast = n / (time.perf_counter() - fast_t)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64->u32", "data": "synthetic",
+        "config": {"workload": "eval7_stream: Philox-seeded random 7-card hands (BASELINE config 1 generator), "
+                               "bounded sample of %d hands per step" % n},
+        "cpu_baseline": {"value": value, "unit": "evals/s", "cores": cores, "kind": "port",
+                         "sample": "%d hands per step, literal port of hand_evaluator.clj (21 subsets x naive evaluator)" % n,
+                         "fast_bitmask_oracle_evals_per_s": fast},
+        "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference Clojure itself is unavailable on this box (no JVM); this is its algorithm restated in C",
+    }
+    print(json.dumps(line))
+
+
+def timed_region(torch, dist, world, fn, steps, warmup):
+    """W untimed + K timed calls of fn(), CUDA events on the current stream, barrier + synchronize on both
+    sides, max over ranks.  returns total milliseconds of the K steps."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def wall_region(torch, dist, world, fn, steps, warmup):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fn()
+    torch.cuda.synchronize()
+    ms = 1e3 * (time.perf_counter() - t0)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import mcb200_loader
+    pkg = mcb200_loader.load()
+    E, api = pkg.engine, pkg.api
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: libmcpoker has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    E.init(devices=[local])
+    L = E.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    hbm_peak, sm_max_mhz, peak_src = load_peaks()
+    sms = torch.cuda.get_device_properties(local).multi_processor_count
+
+    # ---- K1 (headline): resident batch, generated on the device with the config-1 generator ----------
+    n = 1 << args.batch_log2
+    masks = torch.empty(n, dtype=torch.int64, device="cuda")
+    keys = torch.empty(n, dtype=torch.int32, device="cuda")
+    E.check(L.mc_random_hands_dev(SEED, rank * n, n, 7, masks.data_ptr(), stream))
+    launches = [0]
+
+    def k1_step(fmt=E.KEY_NIBBLE):
+        E.check(L.mc_eval7_batch_dev_fmt(masks.data_ptr(), n, keys.data_ptr(), fmt, stream))
+        launches[0] += 1
+
+    sampler = ClockSampler(local)
+    for _ in range(args.warmup):
+        k1_step()
+    sampler.start()
+    launches[0] = 0
+    ms = timed_region(torch, dist, world, k1_step, args.steps, 0)
+    clocks = sampler.stop()
+    gpu_launches = launches[0]
+    value = world * n * args.steps / (ms * 1e-3)
+    per_launch_ms = ms / args.steps
+    achieved_gbs = n * ALGO_BYTES_PER_EVAL / (per_launch_ms * 1e-3) / 1e9
+    # correctness of what was timed: a slice of the keys against the oracle (outside the timed region)
+    check_n = 1 << 20
+    parity = None
+    if rank == 0:
+        import oracle_lib as oracle
+        got = keys[:check_n].cpu().numpy().view(np.uint32)
+        want = oracle.eval_batch(oracle.random_hands(SEED, 0, check_n), 0)
+        parity = bool(np.array_equal(got, want))
+        if not parity:
+            raise SystemExit("K1 keys differ from the oracle: refusing to report a number")
+    variants = {}
+    for name, fmt in (("packed_key", E.KEY_PACKED), ("nibble_flo", E.KEY_NIBBLE_FLO)):
+        v_ms = timed_region(torch, dist, world, lambda: k1_step(fmt), max(2, args.steps // 2), 1)
+        variants[name] = world * n * max(2, args.steps // 2) / (v_ms * 1e-3)
+
+    # ---- e2e: the host-buffer C-ABI call, pinned memory, H2D + kernel + D2H inside the timed region ----
+    ne = 1 << args.e2e_log2
+    h_masks = torch.empty(ne, dtype=torch.int64).pin_memory()
+    h_keys = torch.empty(ne, dtype=torch.int32).pin_memory()
+    h_masks.copy_(masks[:ne])
+    torch.cuda.synchronize()
+
+    def e2e_step():
+        E.check(L.mc_eval7_batch(h_masks.data_ptr(), ne, h_keys.data_ptr()))
+
+    e2e_steps = max(2, args.steps // 2)
+    e2e_ms = wall_region(torch, dist, world, e2e_step, e2e_steps, 1)
+    e2e_value = world * ne * e2e_steps / (e2e_ms * 1e-3)
+    if rank == 0 and not torch.equal(h_keys[:check_n], keys[:check_n].cpu()):
+        raise SystemExit("e2e keys differ from the device-resident run")
+    del masks, keys
+
+    # ---- other BASELINE configs --------------------------------------------------------------------
+    work = {}
+    f_sm = (clocks.get("sm_mhz") or sm_max_mhz) * 1e6
+    int_peak = sms * 128 * f_sm                                 # thread-level int ops/s at the measured clock
+
+    out = torch.zeros(16, dtype=torch.int64, device="cuda")
+    total7 = 133784560
+    lo7, hi7 = total7 * rank // world, total7 * (rank + 1) // world
+
+    def enum_step():
+        out.zero_()
+        E.check(L.mc_enumerate7_dev(lo7, hi7 - lo7, out.data_ptr(), stream))
+        if world > 1:
+            dist.all_reduce(out, op=dist.ReduceOp.SUM)
+
+    ms2 = timed_region(torch, dist, world, enum_step, 10, 3)
+    hist = out[:9].cpu().tolist()
+    golden7 = [23620800, 58877280, 31456080, 6466680, 5576460, 4051784, 3473184, 224848, 37444]
+    rate2 = total7 * 10 / (ms2 * 1e-3)
+    work["config2_enumerate_c52_7"] = {
+        "hands_per_s": rate2, "ms": ms2 / 10, "histogram_equals_golden": hist == golden7, "sharded_over_ranks": world,
+        "roofline": {"bound": "int_issue", "ops_per_unit": OPS["enum"], "achieved": rate2 * OPS["enum"] / 1e12,
+                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate2 * OPS["enum"] / (world * int_peak)}}
+
+    cnt = torch.zeros(27, dtype=torch.int64, device="cuda")
+    holes2 = (C.c_uint64 * 2)(api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50]))
+    nb = 1712304
+    lob, hib = nb * rank // world, nb * (rank + 1) // world
+
+    def eqx_step():
+        cnt.zero_()
+        E.check(L.mc_equity_exhaustive_dev(holes2, 2, 0, 0, lob, hib - lob, cnt.data_ptr(), stream))
+        if world > 1:
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+
+    ms3 = timed_region(torch, dist, world, eqx_step, 20, 3)
+    c3 = cnt.cpu().tolist()
+    rate3 = nb * 20 / (ms3 * 1e-3)
+    work["config3_aa_vs_kk_exhaustive"] = {
+        "boards_per_s": rate3, "ms": ms3 / 20, "counts_equal_golden": [c3[0], c3[1], c3[9]] == [1388072, 318176, 6056],
+        "roofline": {"bound": "int_issue", "ops_per_unit": OPS["board2"], "achieved": rate3 * OPS["board2"] / 1e12,
+                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate3 * OPS["board2"] / (world * int_peak),
+                     "note": "microseconds of work: launch-bound"}}
+
+    holes9 = (C.c_uint64 * 9)(api.mask_of_ids([12, 25]), 0, 0, 0, 0, 0, 0, 0, 0)
+
+    def mc_run(total_trials):
+        lo, hi = total_trials * rank // world, total_trials * (rank + 1) // world
+        cnt.zero_()
+        E.check(L.mc_equity_mc_dev(holes9, 9, 0, 0, SEED, lo, hi - lo, cnt.data_ptr(), stream))
+        if world > 1:
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+
+    cal = 1 << 28
+    ms_cal = timed_region(torch, dist, world, lambda: mc_run(cal), 1, 1)
+    est_rate = cal / (ms_cal * 1e-3)
+    mc_log2 = args.mc_log2
+    while mc_log2 > 28 and (1 << mc_log2) / est_rate > args.mc_budget_s:
+        mc_log2 -= 1
+    trials = 1 << mc_log2
+    ms4 = timed_region(torch, dist, world, lambda: mc_run(trials), 1, 0)
+    c4 = cnt.cpu().tolist()
+    rate4 = trials / (ms4 * 1e-3)
+    work["config4_mc_9_seats"] = {
+        "trials_per_s": rate4, "evals_per_s": 9 * rate4, "trials": trials, "log2_trials": mc_log2, "ms": ms4,
+        "seat0_equity": (c4[0] + c4[9] / 2) / trials, "counts_sum_ok": all(c4[s] + c4[9 + s] + c4[18 + s] == trials for s in range(9)),
+        "collective": "one NCCL all_reduce(int64 x 27)" if world > 1 else "none (1 rank)",
+        "roofline": {"bound": "int_issue", "ops_per_unit": OPS["mc9"], "achieved": rate4 * OPS["mc9"] / 1e12,
+                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate4 * OPS["mc9"] / (world * int_peak)}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle_lib as oracle
+        v, cores, sample_n, dt = cpu_port_baseline(oracle)
+        t0 = time.perf_counter()
+        fast_n = 1 << 22
+        oracle.eval_batch(oracle.random_hands(SEED, 0, fast_n), 0, 0)
+        cpu = {"value": v, "unit": "evals/s", "cores": cores, "kind": "port",
+               "sample": "%d of the Philox-seeded hands, literal port of hand_evaluator.clj (21 subsets x naive evaluator), %.1f s" % (sample_n, dt),
+               "fast_bitmask_oracle_evals_per_s": fast_n / (time.perf_counter() - t0)}
+
+    if rank == 0:
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "k1_traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("dram_bytes_per_launch_at_bench_size")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": per_launch_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64->u32", "data": "synthetic",
+            "config": {"workload": "eval7_stream (K1): 2^%d Philox-seeded 7-card hands per GPU resident in HBM "
+                                   "(BASELINE config 1 generator at throughput size), nibble keys out" % args.batch_log2,
+                       "hands_per_gpu_per_step": n, "l2": "inputs (2 GiB) + outputs (1 GiB) per step exceed the 126 MB L2",
+                       "parallelism": "independent slices per rank, no data-path collective"},
+            "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+                         "kernel": "eval7_stream_kernel<nibble_table>", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
+                         "int_issue_frac_at_64_ops": (value / world) * OPS["eval"] / int_peak},
+            "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
+                    "hands_per_step": ne, "call": "mc_eval7_batch (pinned host buffers, 3-stage copy/compute pipeline)"},
+            "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
+            "k1_variants_evals_per_s": variants, "workloads": work,
+        }
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch-log2", type=int, default=BATCH_LOG2)
+    ap.add_argument("--e2e-log2", type=int, default=E2E_LOG2)
+    ap.add_argument("--mc-log2", type=int, default=34)
+    ap.add_argument("--mc-budget-s", type=float, default=20.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,286 @@
+"""GPU parity tests (run with -m gpu on a B200): every entry point of the C ABI against the CPU oracle on
+the same inputs -- bit-exact, because the whole path is integer work."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_vectors.json")))
+SG = GOLD["survey_goldens"]
+SEED = 0x5EED5EED
+
+
+def test_native_library_is_loaded(gpu):
+    assert gpu.engine.lib().mc_device_count() >= 1
+    maps = open("/proc/self/maps").read()
+    assert "libmcpoker.so" in maps
+
+
+# ---- the reference's own known-answer vectors, through the mirror of its API -------------------------
+@pytest.mark.parametrize("vec", GOLD["evaluator"], ids=lambda v: "line%d" % v["line"])
+def test_evaluator_reference_vectors(gpu, vec):              # hand_evaluator_test.clj:57-137
+    he, Card = gpu.hand_evaluator, gpu.card.Card
+    suit = {0: "h", 1: "d", 2: "s", 3: "c"}                   # the test file's keywords :h :d :s :c
+    cards = [Card(suit[s], r) for s, r in vec["cards"]]
+    assert he.evaluator(cards) == vec["want"]
+    if vec["shuffle"]:
+        rng = random.Random(vec["line"])
+        for _ in range(5):
+            rng.shuffle(cards)
+            assert he.evaluator(cards) == vec["want"]
+
+
+def test_evaluator_errors(gpu):
+    he, Card = gpu.hand_evaluator, gpu.card.Card
+    with pytest.raises(ValueError):                           # < 5 cards
+        he._value([Card("h", 2), Card("d", 3)])
+    with pytest.raises(gpu.engine.McError):
+        gpu.api.eval_cards([0, 0, 0, 0, 0], [2, 3, 4, 5, 15])
+    with pytest.raises(gpu.engine.McError):
+        gpu.api.eval_cards([0, 0, 0, 0, 4], [2, 3, 4, 5, 6])
+    # no wheel
+    assert he.evaluator([Card("h", 14), Card("d", 2), Card("s", 3), Card("c", 4), Card("h", 5)]) == [0, [14, 5, 4, 3, 2], []]
+
+
+def test_player_to_hand_value_5_6_7_cards(gpu, oracle):       # flop / turn / river, SURVEY Q3
+    he, deck = gpu.hand_evaluator, list(gpu.card.COMPLETE_DECK)
+    rng = random.Random(7)
+    for n_board in (3, 4, 5):
+        for _ in range(10):
+            cs = rng.sample(deck, n_board + 2)
+            board = {"community_cards": cs[:n_board], "hands": {"p": cs[n_board:]}}
+            got = he.player_to_hand_value(board, "p")
+            m = oracle.mask_of([(gpu.card.SUITS.index(c.suit), c.rank) for c in cs])
+            assert got == gpu.api.key_decode(oracle.lib().orc_eval_mask(m))
+
+
+# ---- K1: batch evaluation ------------------------------------------------------------------------
+def test_random_hand_generator_matches_oracle(gpu, oracle):
+    n = 200_000
+    assert np.array_equal(gpu.api.random_hands(SEED, 0, n), oracle.random_hands(SEED, 0, n))
+    assert np.array_equal(gpu.api.random_hands(SEED, 12345, 1000, 5), oracle.random_hands(SEED, 12345, 1000, 5))
+
+
+@pytest.mark.parametrize("fmt", [0, 1, 2], ids=["nibble_table", "packed", "nibble_flo"])
+def test_eval7_batch_config1_one_million_hands(gpu, oracle, fmt):
+    """BASELINE config 1: 1,000,000 Philox-seeded 7-card hands, 100% equal to the oracle"""
+    masks = oracle.random_hands(SEED, 0, 1_000_000)
+    want = oracle.eval_batch(masks, 0)
+    got = gpu.api.eval7_batch(masks, key_format=fmt)
+    if fmt == 1:
+        got = np.array([gpu.api.key_packed_to_nibble(int(k)) for k in got[:20000]], dtype=np.uint32)
+        want = want[:20000]
+        packed = gpu.api.eval7_batch(masks, key_format=1)
+        # packed keys order exactly like nibble keys
+        o1 = np.argsort(packed[:20000], kind="stable")
+        assert np.all(np.diff(want[o1].astype(np.int64)) >= 0)
+    assert np.array_equal(got, want)
+
+
+def test_eval7_batch_edge_cases(gpu, oracle):
+    api = gpu.api
+    assert api.eval7_batch(np.zeros(0, dtype=np.uint64)).shape == (0,)
+    # ragged sizes around the vector width, unaligned views, 5/6-card hands, rank 1, invalid masks
+    base = oracle.random_hands(SEED, 0, 4099)
+    for n in (1, 2, 3, 4, 5, 7, 8, 511, 1025, 4099):
+        assert np.array_equal(api.eval7_batch(base[:n]), oracle.eval_batch(base[:n], 0))
+    assert np.array_equal(api.eval7_batch(base[1:1000]), oracle.eval_batch(base[1:1000], 0))
+    mixed = np.concatenate([oracle.random_hands(SEED, 0, 1000, 5), oracle.random_hands(SEED, 0, 1000, 6)])
+    assert np.array_equal(api.eval7_batch(mixed), oracle.eval_batch(mixed, 0))
+    rank1 = np.array([oracle.mask_of([(0, 1), (1, 2), (2, 3), (3, 5), (0, 4)]),
+                      oracle.mask_of([(0, 1), (1, 1), (2, 1), (3, 1), (0, 3)])], dtype=np.uint64)
+    assert [api.key_decode(k) for k in api.eval7_batch(rank1)] == [[4, [5, 4, 3, 2, 1], []], [7, [1, 1, 1, 1], [3]]]
+    bad = np.array([0, 0b111100, 1 << 0 | 0x7C, 1 << 15 | 0x7C, (1 << 64) - 1, 0xFF << 2], dtype=np.uint64)
+    got = api.eval7_batch(bad)
+    assert np.all(got == 0xFFFFFFFF)
+    assert np.array_equal(got, oracle.eval_batch(bad, 0))
+
+
+def test_eval7_batch_multi_stage_pipeline(gpu, oracle):
+    """more hands than one staging buffer holds (4 Mi): exercises the 3-slot H2D/kernel/D2H pipeline"""
+    n = (1 << 22) * 2 + 12345
+    masks = oracle.random_hands(SEED + 1, 0, n)
+    assert np.array_equal(gpu.api.eval7_batch(masks), oracle.eval_batch(masks, 0))
+
+
+def test_k1_on_structured_hand_families(gpu, oracle):
+    """BASELINE target: 100% rank agreement on every seven-card hand.  Key-by-key here for six families of
+    C(49,4) = 211,876 hands (all hands containing a fixed 3-card prefix); every one of the 133,784,560 hands
+    is covered through the histogram + key checksum of test_enumerate7_goldens (same device evaluator)."""
+    import itertools
+    bits = np.array([oracle.card_bit(i) for i in range(52)], dtype=np.uint64)
+    # all hands that contain a fixed 3-card prefix: C(49,4) = 211,876 each; prefixes spread over the deck
+    for prefix in [(0, 1, 2), (0, 13, 26), (12, 25, 38), (5, 18, 44), (47, 49, 51), (3, 4, 5)]:
+        rest = [i for i in range(52) if i not in prefix]
+        ids = np.array(list(itertools.combinations(rest, 4)), dtype=np.int64)
+        masks = np.bitwise_or.reduce(bits[ids], axis=1) | np.bitwise_or.reduce(bits[list(prefix)])
+        assert np.array_equal(gpu.api.eval7_batch(masks), oracle.eval_batch(masks, 0))
+
+
+# ---- K2: exhaustive enumeration (BASELINE config 2) ---------------------------------------------------
+def test_enumerate7_goldens(gpu):
+    hist, key_sum = gpu.api.enumerate7()
+    assert hist[::-1] == SG["hist7_cat8to0"]
+    assert key_sum == SG["keysum7"]
+    assert sum(hist) == 133784560
+    hist2, none = gpu.api.enumerate7(key_sum=False)          # the fast variant (packed keys only)
+    assert hist2 == hist and none is None
+
+
+def test_enumerate7_ranges_match_oracle_and_add_up(gpu, oracle):
+    total = 133784560
+    cuts = [0, 1, 63, 64, 65, 1_000_003, 77_777_777, total - 5, total]
+    acc, acc_sum = [0] * 9, 0
+    for lo, hi in zip(cuts, cuts[1:]):
+        h, s = gpu.api.enumerate7(lo, hi - lo)
+        if hi - lo <= 2_000_000:
+            ho, so, _ = oracle.enumerate_hands(7, 0, first=lo, count=hi - lo)
+            assert h == ho and s == so
+        acc = [a + b for a, b in zip(acc, h)]
+        acc_sum += s
+    assert acc[::-1] == SG["hist7_cat8to0"] and acc_sum == SG["keysum7"]
+    assert gpu.api.enumerate7(5, 0) == ([0] * 9, 0)
+    with pytest.raises(gpu.engine.McError):
+        gpu.api.enumerate7(total, 1)
+
+
+# ---- K3: exhaustive equity (BASELINE config 3) --------------------------------------------------------
+@pytest.mark.parametrize("name", ["aa_kk_no_shared", "aa_kk_both_shared", "aa_kk_one_shared"])
+def test_equity_exhaustive_aa_vs_kk(gpu, name):
+    g = SG[name]
+    holes = [gpu.api.mask_of_ids(h) for h in g["holes_ids"]]
+    w, t, l, nb = gpu.api.equity_exhaustive(holes)
+    assert nb == 1712304
+    assert (w[0], w[1], t[0], t[1]) == (g["win_a"], g["win_b"], g["tie"], g["tie"])
+    assert l == [w[1], w[0]]
+
+
+def test_equity_exhaustive_multiway_partial_boards_dead_cards(gpu, oracle):
+    rng = random.Random(11)
+    for n_seats, n_board, n_dead in [(2, 3, 0), (3, 3, 2), (9, 3, 0), (4, 4, 1), (6, 5, 0), (3, 2, 0), (2, 1, 3), (5, 4, 0)]:
+        ids = rng.sample(range(52), 2 * n_seats + n_board + n_dead)
+        holes = [gpu.api.mask_of_ids(ids[2 * s:2 * s + 2]) for s in range(n_seats)]
+        board = gpu.api.mask_of_ids(ids[2 * n_seats:2 * n_seats + n_board])
+        dead = gpu.api.mask_of_ids(ids[2 * n_seats + n_board:])
+        w, t, l, nb = gpu.api.equity_exhaustive(holes, board, dead)
+        rc, wo, to, lo, nbo = oracle.equity_exhaustive(holes, board, dead)
+        assert rc == 0 and (w, t, l, nb) == (wo, to, lo, nbo)
+        # board ranges add up
+        if nb > 10:
+            cut = nb // 3
+            w1, t1, l1, _ = gpu.api.equity_exhaustive(holes, board, dead, 0, cut)
+            w2, t2, l2, _ = gpu.api.equity_exhaustive(holes, board, dead, cut, nb - cut)
+            assert [a + b for a, b in zip(w1, w2)] == w and [a + b for a, b in zip(t1, t2)] == t
+
+
+def test_equity_argument_errors(gpu):
+    api, E = gpu.api, gpu.engine
+    aa = api.mask_of_ids([12, 25])
+    for holes, board, dead in [([aa, aa], 0, 0), ([aa, 0], 0, 0), ([aa, api.mask_of_ids([0])], 0, 0),
+                               ([aa], api.mask_of_ids([12]), 0), ([aa], 1, 0), ([aa], api.mask_of_ids(range(6)), 0)]:
+        with pytest.raises(E.McError) as e:
+            api.equity_exhaustive(holes, board, dead)
+        assert e.value.code == E.MC_ERR_INVALID
+
+
+# ---- K4: Monte Carlo equity (BASELINE config 4) -------------------------------------------------------
+def test_equity_mc_bit_exact_vs_oracle_9_seats(gpu, oracle):
+    holes = [gpu.api.mask_of_ids([12, 25])] + [0] * 8
+    n = 1 << 20
+    got = gpu.api.equity_mc(holes, 0, 0, SEED, 0, n)
+    rc, w, t, l = oracle.equity_mc(holes, 0, 0, SEED, 0, n)
+    assert rc == 0 and got == (w, t, l)
+    assert all(a + b + c == n for a, b, c in zip(*got))
+
+
+def test_equity_mc_split_invariance_and_offsets(gpu, oracle):
+    holes = [gpu.api.mask_of_ids([12, 25])] + [0] * 8
+    n = 1 << 18
+    full = gpu.api.equity_mc(holes, 0, 0, SEED, 1 << 33, n)        # counters above 2^32 exercise trial_hi
+    parts = [gpu.api.equity_mc(holes, 0, 0, SEED, (1 << 33) + lo, cnt) for lo, cnt in [(0, 1), (1, 99_999), (100_000, n - 100_000)]]
+    summed = tuple([sum(p[k][s] for p in parts) for s in range(9)] for k in range(3))
+    assert summed == full
+    rc, w, t, l = oracle.equity_mc(holes, 0, 0, SEED, 1 << 33, n)
+    assert full == (w, t, l)
+
+
+def test_equity_mc_other_shapes(gpu, oracle):
+    rng = random.Random(5)
+    api = gpu.api
+    cases = [
+        ([0, 0], 0, 0),                                               # everyone random
+        ([api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50])], 0, 0),   # nothing random but the board
+        ([api.mask_of_ids([0, 1]), 0, api.mask_of_ids([20, 33]), 0], api.mask_of_ids([5, 6, 7]), api.mask_of_ids([40, 41])),
+        ([0] * 9, api.mask_of_ids([2, 16, 30, 44]), 0),
+        ([api.mask_of_ids([3, 4])], 0, 0),
+    ]
+    for holes, board, dead in cases:
+        seed = rng.getrandbits(64)
+        got = api.equity_mc(holes, board, dead, seed, 17, 50_000)
+        rc, w, t, l = oracle.equity_mc(holes, board, dead, seed, 17, 50_000)
+        assert rc == 0 and got == (w, t, l)
+
+
+def test_equity_mc_converges_to_exhaustive(gpu):
+    """AA vs KK by Monte Carlo vs the exact count: within 4 sigma (binomial), the tolerance the spec allows"""
+    api = gpu.api
+    holes = [api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50])]
+    n = 1 << 24
+    w, t, l = api.equity_mc(holes, 0, 0, 999, 0, n)
+    p = SG["aa_kk_no_shared"]["win_a"] / 1712304
+    sigma = (p * (1 - p) / n) ** 0.5
+    assert abs(w[0] / n - p) < 4 * sigma
+
+
+# ---- showdown (gameplay.clj:118-133) ------------------------------------------------------------------
+def test_showdown_groups(gpu, oracle):
+    import ctypes as C
+    rng = random.Random(3)
+    for n_seats in (1, 2, 5, 9):
+        for n_board in (3, 4, 5):
+            ids = rng.sample(range(52), 2 * n_seats + n_board)
+            holes = [gpu.api.mask_of_ids(ids[2 * s:2 * s + 2]) for s in range(n_seats)]
+            board = gpu.api.mask_of_ids(ids[2 * n_seats:])
+            keys, winners, group_of, n_groups = gpu.api.showdown(board, holes)
+            want = [oracle.lib().orc_eval_mask(board | h) for h in holes]
+            assert keys == want
+            g = (C.c_int * n_seats)()
+            ng = oracle.lib().orc_group_winners((C.c_uint32 * n_seats)(*want), n_seats, g)
+            assert list(g) == group_of and ng == n_groups
+            assert winners == sum(1 << s for s in range(n_seats) if want[s] == max(want))
+    # a split pot: both play the board
+    board = gpu.api.mask_of_ids([8, 9, 10, 11, 12])                   # hearts 10..A: royal flush on board
+    keys, winners, group_of, n_groups = gpu.api.showdown(board, [gpu.api.mask_of_ids([13, 14]), gpu.api.mask_of_ids([26, 27])])
+    assert winners == 0b11 and group_of == [0, 0] and n_groups == 1 and gpu.api.key_decode(keys[0])[0] == 8
+    with pytest.raises(gpu.engine.McError) as e:                      # pre-flop showdown: SURVEY Q3
+        gpu.api.showdown(0, [gpu.api.mask_of_ids([13, 14])])
+    assert e.value.code == gpu.engine.MC_ERR_TOO_FEW
+
+
+def test_end_game_ranking_mirror(gpu):
+    Card = gpu.card.Card
+    community = [Card("hearts", 2), Card("diamonds", 2), Card("spades", 9), Card("clubs", 11), Card("hearts", 5)]
+    hands = {"a": [Card("spades", 2), Card("clubs", 9)], "b": [Card("hearts", 14), Card("diamonds", 13)],
+             "c": [Card("spades", 14), Card("clubs", 13)]}
+    values, groups = gpu.gameplay.end_game_ranking(community, hands)
+    assert values["a"] == [6, [2, 2, 2, 9, 9], []]
+    assert values["b"] == values["c"] == [1, [2, 2], [14, 13, 11]]
+    assert groups == [{"a"}, {"b", "c"}]
+
+
+# ---- K5: preflop matrix cells (BASELINE config 5) ------------------------------------------------------
+def test_preflop_cells(gpu, oracle):
+    import ctypes as C
+    g = SG["cell_AA_KK"]
+    cells = [(168, 154), (154, 168), (168, 168), (13 * 12 + 11, 13 * 0 + 5)]     # AA-KK, KK-AA, AA-AA, AKs-72o
+    got = gpu.api.preflop_cells(cells)
+    assert got[0].tolist() == [g["win"], g["tie"], g["loss"]]
+    assert got[1].tolist() == [g["loss"], g["tie"], g["win"]]
+    assert got[2][0] == got[2][2] and got[2].sum() == 6 * 1712304
+    wtl = (C.c_int64 * 3)()
+    assert oracle.lib().orc_preflop_cell(cells[3][0], cells[3][1], 0, wtl) == 0
+    assert got[3].tolist() == list(wtl)
