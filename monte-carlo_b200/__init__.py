@@ -8,5 +8,6 @@ repo root, which registers it as the module `monte_carlo_b200`.
   card            mirror of montecarlo.card            (card.clj)
   hand_evaluator  mirror of montecarlo.hand-evaluator  (hand_evaluator.clj) -- same names, GPU-backed
   gameplay        mirror of the showdown part of montecarlo.gameplay (gameplay.clj:104-133)
+  sharding        index-range split across ranks + the one all-reduce of counts
 """
-from . import engine, api, card, hand_evaluator, gameplay  # noqa: F401
+from . import engine, api, card, hand_evaluator, gameplay, sharding  # noqa: F401
