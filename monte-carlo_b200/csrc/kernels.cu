@@ -9,6 +9,7 @@
 // with warp REDUX / shuffles -> shared memory -> a handful of 64-bit global atomics per block.
 #include "kernels.cuh"
 #include "eval.cuh"
+#include "eval_tbl.cuh"
 #include "philox.cuh"
 
 namespace mcp {
@@ -106,8 +107,10 @@ constexpr int K1_THREADS = 512;
 template <int MODE>
 __device__ __forceinline__ uint32_t k1_key(uint64_t m, const uint32_t *T, const uint4 *cc) {
     const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
-    uint32_t k = eval_packed(lo, hi);
-    if (MODE == K1_NIBBLE_TABLE) k = nibble_from_packed_tbl(k, T, cc);
+    uint32_t k;
+    // lanes are clipped to the rank bits so that an invalid mask can never index outside the table
+    if (MODE == K1_NIBBLE_TABLE) k = eval_nibble_tbl<14>(lo & 0x7FFE7FFEu, hi & 0x7FFE7FFEu, T, reinterpret_cast<const uint32_t *>(cc));
+    else k = eval_packed(lo, hi);
     if (MODE == K1_NIBBLE_FLO) k = packed_to_nibble(k);
     const uint32_t n = (uint32_t)(__popc(lo) + __popc(hi));
     const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
@@ -121,8 +124,7 @@ eval7_stream_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ k
     uint32_t *T = smem;
     uint4 *cc = reinterpret_cast<uint4 *>(smem + NIB_ENTRIES);
     if (MODE == K1_NIBBLE_TABLE) {
-        fill_nib_table(T);
-        if (threadIdx.x < 9) cc[threadIdx.x] = CAT_CONST[threadIdx.x];
+        fill_nib_table_v2<14>(T, cc);
         __syncthreads();
     }
     const size_t npair = n >> 1;
@@ -154,8 +156,7 @@ eval7_scalar_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ k
     uint32_t *T = smem;
     uint4 *cc = reinterpret_cast<uint4 *>(smem + NIB_ENTRIES);
     if (MODE == K1_NIBBLE_TABLE) {
-        fill_nib_table(T);
-        if (threadIdx.x < 9) cc[threadIdx.x] = CAT_CONST[threadIdx.x];
+        fill_nib_table_v2<14>(T, cc);
         __syncthreads();
     }
     const size_t stride = (size_t)gridDim.x * blockDim.x;

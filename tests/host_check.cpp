@@ -5,6 +5,8 @@
 #include <cstdlib>
 #include <cstring>
 #include "../monte-carlo_b200/csrc/eval.cuh"
+#include "../monte-carlo_b200/csrc/eval_tbl.cuh"
+#include <vector>
 #include "../oracle/mc_oracle.h"
 
 static uint64_t BINOM[65][9];
@@ -20,6 +22,11 @@ int main(int argc, char **argv) {
     for (int n = 0; n <= 64; n++) for (int k = 0; k <= 8; k++) BINOM[n][k] = k == 0 ? 1 : (n == 0 ? 0 : BINOM[n - 1][k - 1] + BINOM[n - 1][k]);
     int ncards = use56 ? 56 : 52, per = use56 ? 14 : 13, base = use56 ? 1 : 2;
     uint64_t bad = 0, total_all = 0;
+    // the shared-memory table of eval_tbl.cuh, built on the host with the same entry function
+    std::vector<uint32_t> T14(1 << 14), T13(1 << 13), CC(36);
+    for (uint32_t x = 0; x < (1u << 14); x++) T14[x] = mcp::nib_entry(x, 1);
+    for (uint32_t x = 0; x < (1u << 13); x++) T13[x] = mcp::nib_entry(x, 2);
+    for (int c = 0; c < 9; c++) { uint32_t v[4]; mcp::cat_consts(c, v); for (int i = 0; i < 4; i++) CC[4 * c + i] = v[i]; }
     for (int k = 5; k <= (use56 ? 6 : 7); k++) {
         uint64_t total = BINOM[ncards][k];
         uint64_t kbad = 0;
@@ -34,6 +41,9 @@ int main(int argc, char **argv) {
                 uint32_t want = orc_eval_mask(m);
                 uint32_t pk = mcp::eval_packed(m);
                 uint32_t got = mcp::packed_to_nibble(pk);
+                uint32_t t14 = mcp::eval_nibble_tbl<14>((uint32_t)m, (uint32_t)(m >> 32), T14.data(), CC.data());
+                uint32_t t13 = use56 ? want : mcp::eval_nibble_tbl<13>((uint32_t)m, (uint32_t)(m >> 32), T13.data(), CC.data());
+                if (t14 != want || t13 != want) got = t14 != want ? t14 : t13;
                 if (got != want || !mcp::valid_hand(m)) { if (kbad < 5) fprintf(stderr, "MISMATCH k=%d mask=%016llx want=%06x got=%06x packed=%08x\n", k, (unsigned long long)m, want, got, pk); kbad++; }
                 next(c, k, ncards);
             }
