@@ -32,6 +32,16 @@ __global__ void __launch_bounds__(1024) k(uint32_t *out, long long *cyc, uint32_
             if (OP == 8) { asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c));
                            asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c)); }   // alu+fma mix
             if (OP == 9) asm volatile("shl.b32 %0, %0, 1;" : "+r"(a[i]));
+            if (OP == 11) asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+            if (OP == 12) asm volatile("min.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+            if (OP == 13) asm volatile("add.u32 %0, %0, %1; add.u32 %0, %0, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+            if (OP == 14) asm volatile("shr.u32 %0, %0, 1;" : "+r"(a[i]));
+            if (OP == 15) { asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c));
+                            asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b)); }
+            if (OP == 16) { asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c));
+                            asm volatile("popc.b32 %0, %0;" : "+r"(a[i])); }
+            if (OP == 17) asm volatile("mad.lo.u32 %0, %0, 1, %1;" : "+r"(a[i]) : "r"(b));
+            if (OP == 18) asm volatile("{.reg .pred p; setp.ne.u32 p, %1, 0; @p mov.u32 %0, %2;}" : "+r"(a[i]) : "r"(b), "r"(c));
             if (OP == 10) { asm volatile("{.reg .pred p; setp.gt.u32 p, %0, %1; selp.u32 %0, %0, %2, p;}" : "+r"(a[i]) : "r"(b), "r"(c)); }
         }
     }
@@ -71,6 +81,8 @@ int main() {
     int sms = p.multiProcessorCount;
     run<0>("LOP3", 1, sms); run<1>("IADD", 1, sms); run<2>("SHF", 1, sms); run<9>("SHL imm", 1, sms);
     run<6>("PRMT", 1, sms); run<3>("POPC", 1, sms); run<4>("FLO (bfind)", 1, sms); run<5>("IMAD", 1, sms);
-    run<10>("ISETP+SEL", 2, sms); run<8>("LOP3+IMAD mix", 2, sms); run<7>("LDS random (8192 words)", 1, sms);
+    run<10>("ISETP+SEL", 2, sms); run<11>("IMAD.HI (mul.hi)", 1, sms); run<12>("VIMNMX (min)", 1, sms);
+    run<13>("IADD x2 (3-input?)", 2, sms); run<14>("SHR imm", 1, sms); run<15>("LOP3+IMAD.HI mix", 2, sms);
+    run<16>("LOP3+POPC mix", 2, sms); run<17>("mad.lo x*1+b", 1, sms); run<18>("ISETP+@p MOV", 2, sms); run<8>("LOP3+IMAD mix", 2, sms); run<7>("LDS random (8192 words)", 1, sms);
     return 0;
 }

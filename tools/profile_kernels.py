@@ -16,6 +16,7 @@ E.init(devices=[0])
 L = E.lib()
 st = torch.cuda.current_stream().cuda_stream
 log2 = int(sys.argv[1]) if len(sys.argv) > 1 else 26
+which = sys.argv[2] if len(sys.argv) > 2 else "all"
 n = 1 << log2
 masks = torch.empty(n, dtype=torch.int64, device="cuda")
 keys = torch.empty(n, dtype=torch.int32, device="cuda")
@@ -24,6 +25,10 @@ for rep in range(2):
     for fmt in (E.KEY_NIBBLE, E.KEY_PACKED, E.KEY_NIBBLE_FLO):
         E.check(L.mc_eval7_batch_dev_fmt(masks.data_ptr(), n, keys.data_ptr(), fmt, st))
 out = torch.zeros(16, dtype=torch.int64, device="cuda")
+if which == "k1":
+    torch.cuda.synchronize()
+    print("ok k1")
+    sys.exit(0)
 for rep in range(2):
     E.check(L.mc_enumerate7_dev(0, 133784560, out.data_ptr(), st))
 cnt = torch.zeros(27, dtype=torch.int64, device="cuda")
