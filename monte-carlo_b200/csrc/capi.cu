@@ -6,6 +6,7 @@
 #include "eval.cuh"
 #include "kernels.cuh"
 #include "philox.cuh"
+#include "hashtab_build.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -43,6 +44,8 @@ struct DevCtx {
     unsigned long long *h_small = nullptr;        // pinned mirror
     Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
     long long *d_wtl = nullptr;
+    DeviceTables tb;                              // perfect-hash evaluator tables (hashtab.cuh), built at init
+    void *d_tables = nullptr;                     // one allocation: blob | card keys | nibble keys
 
     ~DevCtx() {
         if (device < 0) return;
@@ -56,6 +59,7 @@ struct DevCtx {
         if (h_small) cudaFreeHost(h_small);
         if (d_matchups) cudaFree(d_matchups);
         if (d_wtl) cudaFree(d_wtl);
+        if (d_tables) cudaFree(d_tables);
         if (stream) cudaStreamDestroy(stream);
     }
 };
@@ -69,6 +73,56 @@ int make_info(int dev, DeviceInfo *out) {
     CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (major != 10) return fail(MC_ERR_NO_DEVICE, "device " + std::to_string(dev) + " is not sm_100 (B200); this library has no other code path");
     out->device = dev; out->sm_count = sms;
+    return MC_OK;
+}
+
+// Hash tables of hashtab.cuh.  The representative hands are evaluated on the device with the bit-plane
+// evaluator (K1, packed keys); the host only lays the results out (hashtab_build.h).
+std::unique_ptr<HashTables> g_tables;
+
+int build_tables(DevCtx &c) {
+    std::vector<HashRep> reps;
+    ht_representatives(HT_MUL_CANDIDATES[0], &reps);
+    const size_t n = reps.size();
+    std::vector<uint64_t> masks(n);
+    std::vector<uint32_t> packed(n);
+    for (size_t i = 0; i < n; i++) masks[i] = reps[i].mask;
+    uint64_t *d_m = nullptr; uint32_t *d_k = nullptr;
+    CU(cudaMalloc(&d_m, n * sizeof(uint64_t)));
+    CU(cudaMalloc(&d_k, n * sizeof(uint32_t)));
+    CU(cudaMemcpyAsync(d_m, masks.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, c.stream));
+    CU(launch_eval7_stream(d_m, n, d_k, K1_PACKED, c.info, c.stream));
+    CU(cudaMemcpyAsync(packed.data(), d_k, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    cudaFree(d_m); cudaFree(d_k);
+    std::unique_ptr<HashTables> T(new HashTables());
+    std::string err = "no multiplier tried";
+    for (uint32_t mul : HT_MUL_CANDIDATES) {
+        ht_representatives(mul, &reps);
+        err = ht_build(reps, packed, mul, T.get());
+        if (err.empty()) break;
+    }
+    if (!err.empty()) return fail(MC_ERR_CUDA, "hash table construction failed: " + err);
+    g_tables = std::move(T);
+    return MC_OK;
+}
+
+int upload_tables(DevCtx &c) {
+    const HashTables &T = *g_tables;
+    const size_t off_card = sizeof(HashBlob), off_nib = off_card + sizeof(T.card);
+    const size_t total = off_nib + T.nib_keys.size() * sizeof(uint32_t);
+    CU(cudaMalloc(&c.d_tables, total));
+    unsigned char *base = static_cast<unsigned char *>(c.d_tables);
+    CU(cudaMemcpyAsync(base, &T.blob, sizeof(HashBlob), cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_card, T.card, sizeof(T.card), cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_nib, T.nib_keys.data(), T.nib_keys.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
+    CU(cudaStreamSynchronize(c.stream));
+    c.tb.d_blob = reinterpret_cast<const HashBlob *>(base);
+    c.tb.d_card = reinterpret_cast<const CardKey *>(base + off_card);
+    c.tb.d_nib = reinterpret_cast<const uint32_t *>(base + off_nib);
+    c.tb.h_card = T.card;
+    for (int i = 0; i < 10; i++) c.tb.cat_base.v[i] = T.cat_base[i];
+    c.tb.n_classes = (uint32_t)T.nib_keys.size();
     return MC_OK;
 }
 
@@ -91,6 +145,9 @@ int init_devices(const int *ids, int n) {
         CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
         CU(cudaMalloc(&c->d_small, SMALL_WORDS * sizeof(unsigned long long)));
         CU(cudaHostAlloc(&c->h_small, SMALL_WORDS * sizeof(unsigned long long), cudaHostAllocDefault));
+        if (!g_tables) { rc = build_tables(*c); if (rc) return rc; }
+        rc = upload_tables(*c);
+        if (rc) return rc;
         g_ctx.push_back(std::move(c));
     }
     return MC_OK;
@@ -107,6 +164,14 @@ int current_info(DeviceInfo *out) {
     CU(cudaGetDevice(&dev));
     for (auto &c : g_ctx) if (c->device == dev) { *out = c->info; return MC_OK; }
     return make_info(dev, out);
+}
+
+// tables of the calling thread's current device (the hash kernels need mc_init to have run for it)
+int current_tables(DeviceInfo *di, const DeviceTables **tb) {
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    for (auto &c : g_ctx) if (c->device == dev) { *di = c->info; *tb = &c->tb; return MC_OK; }
+    return fail(MC_ERR_NOT_INIT, "mc_init / mc_init_devices has not been called for the current device");
 }
 
 int ensure_slots(DevCtx &c) {
@@ -190,6 +255,7 @@ int mc_init_devices(const int *device_ids, int n) {
 void mc_shutdown(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     g_ctx.clear();
+    g_tables.reset();
 }
 int mc_device_count(void) { return (int)g_ctx.size(); }
 
@@ -357,20 +423,19 @@ int mc_enumerate7_dev(uint64_t first, uint64_t count, uint64_t *d_out, void *str
     const uint64_t total = host_binom(52, 7);
     if (first > total || count > total - first) return fail(MC_ERR_INVALID, "combination range out of bounds");
     if (!d_out) return fail(MC_ERR_INVALID, "null device buffer");
-    DeviceInfo di;
-    int rc = current_info(&di);
+    DeviceInfo di; const DeviceTables *tb;
+    int rc = current_tables(&di, &tb);
     if (rc) return rc;
-    CU(launch_enum7(first, count, reinterpret_cast<unsigned long long *>(d_out), false, di, (cudaStream_t)stream));
+    CU(launch_enum7_hash(first, count, reinterpret_cast<unsigned long long *>(d_out), *tb, di, (cudaStream_t)stream));
     return MC_OK;
 }
 int mc_enumerate7_range(uint64_t first, uint64_t count, uint64_t hist[9], uint64_t *key_sum) {
     const uint64_t total = host_binom(52, 7);
     if (first > total || count > total - first) return fail(MC_ERR_INVALID, "combination range out of bounds");
     if (!hist) return fail(MC_ERR_INVALID, "hist is null");
-    unsigned long long sum[11];
-    const bool nib = key_sum != nullptr;
-    int rc = sharded_small_job(count, 11, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
-        CU(launch_enum7(first + lo, cnt, c.d_small, nib, c.info, c.stream));
+    unsigned long long sum[10];
+    int rc = sharded_small_job(count, 10, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        CU(launch_enum7_hash(first + lo, cnt, c.d_small, c.tb, c.info, c.stream));
         return MC_OK;
     });
     if (rc) return rc;
@@ -394,10 +459,10 @@ int mc_equity_exhaustive_dev(const uint64_t *hole_masks, int n_seats, uint64_t b
     const uint64_t total = board_count(a);
     if (first_board > total || n_boards_in > total - first_board) return fail(MC_ERR_INVALID, "board range out of bounds");
     if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
-    DeviceInfo di;
-    rc = current_info(&di);
+    DeviceInfo di; const DeviceTables *tb;
+    rc = current_tables(&di, &tb);
     if (rc) return rc;
-    CU(launch_equity_exhaustive(a, first_board, n_boards_in, reinterpret_cast<long long *>(d_counts), di, (cudaStream_t)stream));
+    CU(launch_equity_exhaustive_hash(a, first_board, n_boards_in, reinterpret_cast<long long *>(d_counts), *tb, di, (cudaStream_t)stream));
     return MC_OK;
 }
 int mc_equity_exhaustive_range(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
@@ -409,7 +474,7 @@ int mc_equity_exhaustive_range(const uint64_t *hole_masks, int n_seats, uint64_t
     if (first_board > total || n_boards_in > total - first_board) return fail(MC_ERR_INVALID, "board range out of bounds");
     unsigned long long sum[27];
     rc = sharded_small_job(n_boards_in, 27, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
-        CU(launch_equity_exhaustive(a, first_board + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.info, c.stream));
+        CU(launch_equity_exhaustive_hash(a, first_board + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.tb, c.info, c.stream));
         return MC_OK;
     });
     if (rc) return rc;
@@ -437,10 +502,10 @@ int mc_equity_mc_dev(const uint64_t *hole_masks, int n_seats, uint64_t board_mas
     int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, true, &a, nullptr);
     if (rc) return rc;
     if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
-    DeviceInfo di;
-    rc = current_info(&di);
+    DeviceInfo di; const DeviceTables *tb;
+    rc = current_tables(&di, &tb);
     if (rc) return rc;
-    if (n_trials) CU(launch_equity_mc(a, seed, first_trial, n_trials, reinterpret_cast<long long *>(d_counts), di, (cudaStream_t)stream));
+    if (n_trials) CU(launch_equity_mc_fy(a, seed, first_trial, n_trials, reinterpret_cast<long long *>(d_counts), *tb, di, (cudaStream_t)stream));
     return MC_OK;
 }
 int mc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
@@ -450,7 +515,7 @@ int mc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, u
     if (rc) return rc;
     unsigned long long sum[27];
     rc = sharded_small_job(n_trials, 27, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
-        CU(launch_equity_mc(a, seed, first_trial + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.info, c.stream));
+        CU(launch_equity_mc_fy(a, seed, first_trial + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.tb, c.info, c.stream));
         return MC_OK;
     });
     if (rc) return rc;
@@ -533,7 +598,7 @@ int run_matchups(const std::vector<Matchup> &mus, std::vector<long long> *wtl_fu
         CU(cudaMemsetAsync(c.d_wtl, 0, cells * sizeof(long long), c.stream));
         if (!part[d].empty()) {
             CU(cudaMemcpyAsync(c.d_matchups, part[d].data(), part[d].size() * sizeof(Matchup), cudaMemcpyHostToDevice, c.stream));
-            CU(launch_preflop(c.d_matchups, (int)part[d].size(), c.d_wtl, c.info, c.stream));
+            CU(launch_preflop_hash(c.d_matchups, (int)part[d].size(), c.d_wtl, c.tb, c.info, c.stream));
         }
         CU(cudaMemcpyAsync(host[d].data(), c.d_wtl, cells * sizeof(long long), cudaMemcpyDeviceToHost, c.stream));
     }

@@ -1,0 +1,99 @@
+// common.cuh -- device helpers shared by kernels.cu and kernels_hash.cu: binomial table + colex unranking,
+// warp reductions, the per-seat showdown counters and their block-level flush into 64-bit global counts.
+#pragma once
+#include <cstdint>
+#include "kernels.cuh"
+
+namespace mcp {
+
+// ---------------------------------------------------------------------------------------------------
+// small helpers
+// ---------------------------------------------------------------------------------------------------
+__host__ __device__ constexpr uint32_t cbinom(int n, int k) {
+    if (k < 0 || k > n) return 0;
+    unsigned long long r = 1;
+    for (int i = 1; i <= k; i++) r = r * (unsigned long long)(n - k + i) / (unsigned long long)i;
+    return (uint32_t)r;
+}
+
+constexpr int BIN_N = 53, BIN_K = 8;
+
+// shared-memory copy of the binomial table used by colex unranking
+__device__ __forceinline__ void fill_binom(uint32_t *sbin) {
+    for (int i = threadIdx.x; i < BIN_N * BIN_K; i += blockDim.x) {
+        const int n = i / BIN_K, k = i % BIN_K;
+        unsigned long long r = (k <= n) ? 1ull : 0ull;
+        for (int j = 1; j <= k && k <= n; j++) r = r * (unsigned long long)(n - k + j) / (unsigned long long)j;
+        sbin[i] = (uint32_t)r;
+    }
+}
+// colex unrank: idx = sum_i C(c_i, i+1), c_0 < c_1 < ... < c_{K-1} < n
+template <int K>
+__device__ __forceinline__ void colex_unrank(uint32_t idx, int n, const uint32_t *sbin, int (&c)[K]) {
+    int x = n;
+#pragma unroll
+    for (int i = K; i >= 1; i--) {
+        x--;
+        while (sbin[x * BIN_K + i] > idx) x--;
+        c[i - 1] = x;
+        idx -= sbin[x * BIN_K + i];
+    }
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xFFFFFFFFu, v); }
+__device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// showdown of up to nine evaluated seats held in registers (gameplay.clj:127-132): win if sole maximum,
+// tie if the maximum is shared, else loss.  Packed keys order exactly like clojure.core/compare.
+// ---------------------------------------------------------------------------------------------------
+struct SeatCounters {
+    uint32_t win[MAX_SEATS], tie[MAX_SEATS];
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) { win[s] = 0; tie[s] = 0; }
+    }
+    __device__ __forceinline__ void add(const uint32_t (&key)[MAX_SEATS], int n_seats) {
+        uint32_t best = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) if (s < n_seats) best = max(best, key[s]);
+        int nbest = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) if (s < n_seats) nbest += (key[s] == best);
+        const bool solo = nbest == 1;
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) if (s < n_seats) {
+            const bool b = key[s] == best;
+            win[s] += (b && solo);
+            tie[s] += (b && !solo);
+        }
+    }
+};
+
+// block-level reduction of the per-thread counters into d_counts = win[9] tie[9] loss[9] (loss = n - win - tie)
+__device__ __forceinline__ void flush_counters(const SeatCounters &sc, uint32_t my_units, int n_seats,
+                                               unsigned long long *sred /*19*/, long long *d_counts) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int s = 0; s < MAX_SEATS; s++) if (s < n_seats) {
+        const uint32_t w = warp_sum(sc.win[s]), t = warp_sum(sc.tie[s]);
+        if (lane == 0) { if (w) atomicAdd(&sred[s], (unsigned long long)w); if (t) atomicAdd(&sred[9 + s], (unsigned long long)t); }
+    }
+    const uint32_t u = warp_sum(my_units);
+    if (lane == 0) atomicAdd(&sred[18], (unsigned long long)u);
+    __syncthreads();
+    if ((int)threadIdx.x < n_seats) {
+        const int s = threadIdx.x;
+        const unsigned long long w = sred[s], t = sred[9 + s], n = sred[18];
+        unsigned long long *o = reinterpret_cast<unsigned long long *>(d_counts);
+        if (w) atomicAdd(&o[s], w);
+        if (t) atomicAdd(&o[9 + s], t);
+        if (n - w - t) atomicAdd(&o[18 + s], n - w - t);
+    }
+}
+
+}  // namespace mcp

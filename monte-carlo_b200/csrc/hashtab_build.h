@@ -1,0 +1,125 @@
+// hashtab_build.h -- host-side construction of the perfect-hash tables of hashtab.cuh.  Pure table layout work:
+// it never evaluates a hand.  The caller supplies, for every 7-card rank multiset and every 5..7-card flush lane,
+// the packed key of a representative hand (mc_init computes them ON THE GPU with the bit-plane evaluator of
+// eval.cuh; tests/host_check.cpp computes them with the same header compiled for the host), and gets back
+//   blob      D / F / V of hashtab.cuh, values = class codes (cat << 12 | index inside the category)
+//   nib_keys  dense class index -> public nibble key (ascending)
+//   cat_base  dense index of the first class of each category (cat_base[9] = number of classes)
+#pragma once
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "hashtab.cuh"
+
+namespace mcp {
+
+// premultiplied key of rank r (2..14) for multiplier mul
+inline uint32_t rank_key(int r, uint32_t mul) { return RK_RAW[r - 2] * mul; }
+
+struct HashRep { uint64_t mask; uint32_t t; uint32_t flush_index; };   // flush_index = 0xFFFFFFFF for rank-pattern reps
+
+// representative hands: one per 7-card rank multiset (suits dealt round-robin so that no suit holds more than two
+// cards), then one per rank set of 5, 6 or 7 cards in a single suit
+inline void ht_representatives(uint32_t mul, std::vector<HashRep> *out) {
+    out->clear();
+    int cnt[13];
+    struct Rec {
+        static void go(int r, int left, int *cnt, uint32_t mul, std::vector<HashRep> *out) {
+            if (r == 13) {
+                if (left) return;
+                HashRep h{0, 0, 0xFFFFFFFFu};
+                int k = 0;
+                for (int i = 0; i < 13; i++)
+                    for (int c = 0; c < cnt[i]; c++, k++) {
+                        h.mask |= 1ull << (16 * (k & 3) + i + 2);
+                        h.t += rank_key(i + 2, mul);
+                    }
+                out->push_back(h);
+                return;
+            }
+            for (int c = 0; c <= (left < 4 ? left : 4); c++) { cnt[r] = c; go(r + 1, left - c, cnt, mul, out); }
+            cnt[r] = 0;
+        }
+    };
+    std::memset(cnt, 0, sizeof cnt);
+    Rec::go(0, 7, cnt, mul, out);
+    for (uint32_t x = 0; x < (uint32_t)HT_FLUSH; x++) {
+        const int n = __builtin_popcount(x);
+        if (n < 5 || n > 7) continue;
+        out->push_back(HashRep{(uint64_t)x << 2, 0, x});
+    }
+}
+
+struct HashTables {
+    HashBlob blob;
+    std::vector<uint32_t> nib_keys;
+    uint32_t cat_base[10];
+    uint32_t mul;
+    CardKey card[64];                 // by bit position
+};
+
+// packed[i] = packed key (eval.cuh) of reps[i].  Returns "" or an error description.
+inline std::string ht_build(const std::vector<HashRep> &reps, const std::vector<uint32_t> &packed, uint32_t mul,
+                            HashTables *T) {
+    if (reps.size() != packed.size()) return "size mismatch";
+    std::vector<uint32_t> keys(packed);
+    std::sort(keys.begin(), keys.end());
+    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+    std::vector<uint16_t> code(keys.size());
+    T->nib_keys.resize(keys.size());
+    for (int c = 0; c <= 9; c++) T->cat_base[c] = (uint32_t)keys.size();
+    uint32_t prev_cat = 99, idx = 0;
+    for (size_t i = 0; i < keys.size(); i++) {
+        const uint32_t cat = keys[i] >> 28;
+        if (cat > 8) return "a representative evaluated to an invalid key";
+        if (cat != prev_cat) { idx = 0; prev_cat = cat; T->cat_base[cat] = (uint32_t)i; }
+        if (idx >= 4096) return "more than 4096 classes in one category";
+        code[i] = (uint16_t)(cat << 12 | idx++);
+        T->nib_keys[i] = packed_to_nibble(keys[i]);
+    }
+    for (int c = 8; c >= 0; c--) if (T->cat_base[c] == keys.size() && c < 9) T->cat_base[c] = T->cat_base[c + 1];
+    auto code_of = [&](uint32_t pk) { return code[std::lower_bound(keys.begin(), keys.end(), pk) - keys.begin()]; };
+
+    std::memset(&T->blob, 0, sizeof T->blob);
+    std::vector<std::vector<std::pair<uint32_t, uint16_t>>> bucket(HT_BUCKETS);     // (t >> 16, code)
+    size_t n_multi = 0;
+    for (size_t i = 0; i < reps.size(); i++) {
+        if (reps[i].flush_index != 0xFFFFFFFFu) { T->blob.F[reps[i].flush_index] = code_of(packed[i]); continue; }
+        bucket[ht_bucket(reps[i].t)].push_back({reps[i].t >> 16, code_of(packed[i])});
+        n_multi++;
+    }
+    if (n_multi != (size_t)HT_N_MULTISETS) return "unexpected number of rank multisets";
+    std::vector<int> order(HT_BUCKETS);
+    for (int i = 0; i < HT_BUCKETS; i++) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return bucket[a].size() != bucket[b].size() ? bucket[a].size() > bucket[b].size() : a < b; });
+    std::vector<char> used(HT_SLOTS, 0);
+    for (int b : order) {
+        auto &items = bucket[b];
+        if (items.empty()) break;
+        for (size_t i = 0; i < items.size(); i++)
+            for (size_t j = i + 1; j < items.size(); j++)
+                if (items[i].first == items[j].first) return "two multisets share bucket and slot: pick another multiplier";
+        uint32_t d = 0;
+        for (; d <= (uint32_t)HT_MAX_DISP; d++) {
+            bool ok = true;
+            for (auto &it : items) if (used[it.first + d]) { ok = false; break; }
+            if (ok) break;
+        }
+        if (d > (uint32_t)HT_MAX_DISP) return "displacement search failed: pick another multiplier";
+        T->blob.D[b] = (uint16_t)d;
+        for (auto &it : items) { used[it.first + d] = 1; T->blob.V[it.first + d] = it.second; }
+    }
+    T->mul = mul;
+    for (int p = 0; p < 64; p++) {
+        const int r = p & 15, s = p >> 4;
+        T->card[p].rk = (r >= 2 && r <= 14) ? rank_key(r, mul) : 0u;
+        T->card[p].sn = 1u << (4 * s);
+    }
+    return "";
+}
+
+constexpr uint32_t HT_MUL_CANDIDATES[] = {0x165667B1u, 0x27D4EB2Fu, 0x85EBCA6Bu, 0xC2B2AE35u, 0x9E3779B1u};
+
+}  // namespace mcp

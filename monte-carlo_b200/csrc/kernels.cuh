@@ -45,6 +45,27 @@ struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weig
 cudaError_t launch_preflop(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
                            const DeviceInfo &di, cudaStream_t st);
 
+// ---- kernels on the additive-key / perfect-hash evaluator (kernels_hash.cu, hashtab.cuh) ----------------
+struct HashBlob;
+struct CardKey;
+struct CatBase { uint32_t v[10]; };          // dense class index of the first class of each category; v[9] = #classes
+struct DeviceTables {
+    const HashBlob *d_blob = nullptr;        // device: D / F / V
+    const CardKey *d_card = nullptr;         // device: 64 entries by bit position
+    const uint32_t *d_nib = nullptr;         // device: dense class index -> nibble key
+    const CardKey *h_card = nullptr;         // host copy of d_card
+    CatBase cat_base{};
+    uint32_t n_classes = 0;
+};
+cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out /* hist[9], nibble key sum */,
+                              const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+cudaError_t launch_equity_exhaustive_hash(const EquityArgs &a, uint64_t first_board, uint64_t n_boards, long long *d_counts,
+                                          const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                                long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
+                                const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+
 uint64_t host_binom(int n, int k);
 
 }  // namespace mcp

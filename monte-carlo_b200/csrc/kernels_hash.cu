@@ -1,0 +1,596 @@
+// kernels_hash.cu -- the enumeration / equity kernels on the additive-key + perfect-hash evaluator (hashtab.cuh).
+//   K2 enum7_hash          all C(52,7) hands -> category histogram + nibble-key checksum   (BASELINE config 2)
+//   K3 equity_exh_hash     every completion of the board -> win/tie/loss per seat          (config 3; gameplay.clj:127-132)
+//   K5 preflop_hash        suit-canonical matchups x all C(48,5) boards                    (config 5)
+//   K4 equity_mc_fy        Philox Fisher-Yates deal per trial + showdown                   (config 4; board.clj:148,
+//                                                                                           gameplay.clj:63-75,41-54,127-132)
+// One block per SM: the 164 KB hash blob lives in shared memory; a hand is (t, sn, mask) and grows by one card
+// with two integer adds; a 7-card value is two shared-memory loads (hashtab.cuh).  No tensor cores, no HBM
+// traffic besides the table staging and <= 27 64-bit atomics per block.
+#include "kernels.cuh"
+#include "common.cuh"
+#include "hashtab.cuh"
+#include "philox.cuh"
+#include <cstring>
+
+namespace mcp {
+
+struct HandState { uint32_t t, sn, mlo, mhi; };
+__device__ __forceinline__ HandState with_card(const HandState &h, const uint4 &c) {
+    return HandState{h.t + c.x, h.sn + c.y, h.mlo | c.z, h.mhi | c.w};
+}
+__host__ __device__ __forceinline__ uint4 live_entry(const CardKey &k, int pos) {
+    return make_uint4(k.rk, k.sn, pos < 32 ? 1u << pos : 0u, pos >= 32 ? 1u << (pos - 32) : 0u);
+}
+
+// stage the hash blob in shared memory (16-byte loads; the blob stays L2-resident across blocks)
+__device__ __forceinline__ void stage_blob(HashBlob *dst, const HashBlob *__restrict__ src) {
+    const uint4 *g = reinterpret_cast<const uint4 *>(src);
+    uint4 *s = reinterpret_cast<uint4 *>(dst);
+    for (int i = threadIdx.x; i < (int)(sizeof(HashBlob) / 16); i += blockDim.x) s[i] = __ldg(g + i);
+}
+
+// Walks K-subsets of the live list in colex order, keeping the partial hands P[i] = base + cards c[i..K-1] in
+// registers: the common step (lowest card moves) costs one 16-byte shared load and four integer ops.
+template <int K>
+struct Walker {
+    int c[K > 0 ? K : 1];
+    HandState P[K + 1];
+
+    __device__ __forceinline__ void init(uint32_t idx, int nl, const uint32_t *sbin, const uint4 *live, const HandState &base) {
+        P[K] = base;
+        if constexpr (K > 0) {
+            colex_unrank<K>(idx, nl, sbin, c);
+#pragma unroll
+            for (int i = K - 1; i >= 0; i--) P[i] = with_card(P[i + 1], live[c[i]]);
+        }
+    }
+    template <int I>
+    __device__ __forceinline__ void bump(const uint4 *live, int nl) {
+        if constexpr (I < K) {
+            c[I]++;
+            if constexpr (I + 1 < K) {
+                if (c[I] == c[I + 1]) { c[I] = I; bump<I + 1>(live, nl); }
+            } else {
+                if (c[I] >= nl) c[I] = nl;           // past the last subset: live[nl] is a zero entry
+            }
+            P[I] = with_card(P[I + 1], live[c[I]]);
+        }
+    }
+    __device__ __forceinline__ void next(const uint4 *live, int nl) { bump<0>(live, nl); }
+    __device__ __forceinline__ const HandState &hand() const { return P[0]; }
+};
+
+// per-seat win / tie counters of one thread and their reduction into d_counts = win[9] tie[9] loss[9]
+template <int NS>
+struct Tally {
+    uint32_t win[NS], tie[NS], units;
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int s = 0; s < NS; s++) { win[s] = 0; tie[s] = 0; }
+        units = 0;
+    }
+    __device__ __forceinline__ void add(const uint32_t (&key)[NS], int n_seats) {
+        uint32_t best = 0;
+#pragma unroll
+        for (int s = 0; s < NS; s++) if (NS == 2 || s < n_seats) best = max(best, key[s]);
+        int nbest = 0;
+#pragma unroll
+        for (int s = 0; s < NS; s++) if (NS == 2 || s < n_seats) nbest += (key[s] == best);
+        const bool solo = nbest == 1;
+#pragma unroll
+        for (int s = 0; s < NS; s++) if (NS == 2 || s < n_seats) {
+            const bool b = key[s] == best;
+            win[s] += (b && solo);
+            tie[s] += (b && !solo);
+        }
+        units++;
+    }
+    // sred: 19 zeroed u64 in shared memory; seat_of[s] = output seat of counter s
+    __device__ __forceinline__ void flush(int n_seats, unsigned long long *sred, long long *d_counts) {
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int s = 0; s < NS; s++) if (NS == 2 || s < n_seats) {
+            const uint32_t w = warp_sum(win[s]), t = warp_sum(tie[s]);
+            if (lane == 0) { if (w) atomicAdd(&sred[s], (unsigned long long)w); if (t) atomicAdd(&sred[9 + s], (unsigned long long)t); }
+        }
+        const uint32_t u = warp_sum(units);
+        if (lane == 0 && u) atomicAdd(&sred[18], (unsigned long long)u);
+        __syncthreads();
+        if ((int)threadIdx.x < n_seats) {
+            const int s = threadIdx.x;
+            const unsigned long long w = sred[s], t = sred[9 + s], n = sred[18];
+            unsigned long long *o = reinterpret_cast<unsigned long long *>(d_counts);
+            if (w) atomicAdd(&o[s], w);
+            if (t) atomicAdd(&o[9 + s], t);
+            if (n - w - t) atomicAdd(&o[18 + s], n - w - t);
+        }
+    }
+};
+
+constexpr int HASH_THREADS = 512;
+constexpr int LIVE_MAX = 56;
+
+// ---------------------------------------------------------------------------------------------------
+// K3: exhaustive equity over all K-card completions of the board
+// ---------------------------------------------------------------------------------------------------
+struct EqxHashParams {
+    uint32_t h_t[MAX_SEATS], h_sn[MAX_SEATS], h_mlo[MAX_SEATS], h_mhi[MAX_SEATS];   // fixed hole cards per seat
+    HandState base;                     // known community cards, sn biased
+    uint64_t first, count;
+    int n_seats, n_live;
+    uint4 live[LIVE_MAX];               // ascending bit position; entries >= n_live are zero
+};
+
+template <int K, int NS>
+__global__ void __launch_bounds__(HASH_THREADS, 1)
+equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob *__restrict__ g_blob,
+                       long long *__restrict__ d_counts) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *slive = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX);
+    __shared__ unsigned long long sred[19];
+    stage_blob(H, g_blob);
+    fill_binom(sbin);
+    if (threadIdx.x < LIVE_MAX) slive[threadIdx.x] = prm.live[threadIdx.x];
+    if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
+    __syncthreads();
+
+    const int n_seats = prm.n_seats, nl = prm.n_live;
+    Tally<NS> tl; tl.clear();
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t per = (prm.count + nthreads - 1) / nthreads;
+    const uint64_t me = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t lo = me * per < prm.count ? me * per : prm.count;
+    const uint64_t hi = lo + per < prm.count ? lo + per : prm.count;
+    if (lo < hi) {
+        Walker<K> w;
+        w.init((uint32_t)(prm.first + lo), nl, sbin, slive, prm.base);
+        for (uint64_t i = lo; i < hi; i++) {
+            const HandState b = w.hand();
+            uint32_t key[NS];
+#pragma unroll
+            for (int s = 0; s < NS; s++) {
+                key[s] = 0;
+                if (NS == 2 || s < n_seats)
+                    key[s] = ht_class(b.t + prm.h_t[s], b.sn + prm.h_sn[s], b.mlo | prm.h_mlo[s], b.mhi | prm.h_mhi[s],
+                                      H->D, H->F, H->V);
+            }
+            tl.add(key, n_seats);
+            w.next(slive, nl);
+        }
+    }
+    tl.flush(n_seats, sred, d_counts);
+}
+
+static size_t eqx_smem() { return sizeof(HashBlob) + LIVE_MAX * sizeof(uint4) + BIN_N * BIN_K * sizeof(uint32_t); }
+
+static void fill_live(uint64_t live_mask, const CardKey *card, uint4 *live, int *n_live) {
+    int nl = 0;
+    for (int b = 0; b < 64; b++) if ((live_mask >> b) & 1ull) live[nl++] = live_entry(card[b], b);
+    *n_live = nl;
+    for (int i = nl; i < LIVE_MAX; i++) live[i] = make_uint4(0, 0, 0, 0);
+}
+static HandState state_of(uint64_t mask, const CardKey *card, uint32_t sn0) {
+    HandState h{0, sn0, (uint32_t)mask, (uint32_t)(mask >> 32)};
+    for (int b = 0; b < 64; b++) if ((mask >> b) & 1ull) { h.t += card[b].rk; h.sn += card[b].sn; }
+    return h;
+}
+
+template <int K, int NS>
+static cudaError_t launch_eqx(const EqxHashParams &prm, const HashBlob *blob, long long *d_counts, int grid, cudaStream_t st) {
+    auto kern = equity_exh_hash_kernel<K, NS>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
+    if (e != cudaSuccess) return e;
+    kern<<<grid, HASH_THREADS, eqx_smem(), st>>>(prm, blob, d_counts);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_equity_exhaustive_hash(const EquityArgs &a, uint64_t first_board, uint64_t n_boards, long long *d_counts,
+                                          const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (n_boards == 0) return cudaSuccess;
+    EqxHashParams prm;
+    uint64_t used = a.board | a.dead;
+    for (int s = 0; s < MAX_SEATS; s++) {
+        const uint64_t h = s < a.n_seats ? a.hole[s] : 0ull;
+        used |= h;
+        const HandState hs = state_of(h, tb.h_card, 0);
+        prm.h_t[s] = hs.t; prm.h_sn[s] = hs.sn; prm.h_mlo[s] = hs.mlo; prm.h_mhi[s] = hs.mhi;
+    }
+    prm.base = state_of(a.board, tb.h_card, SN_BIAS);
+    prm.first = first_board; prm.count = n_boards; prm.n_seats = a.n_seats;
+    fill_live(DECK_MASK & ~used, tb.h_card, prm.live, &prm.n_live);
+    const int K = 5 - __builtin_popcountll(a.board);
+    uint64_t want = (n_boards + HASH_THREADS - 1) / HASH_THREADS;
+    const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
+    const bool two = a.n_seats == 2;
+#define EQX_CASE(k) case k: return two ? launch_eqx<k, 2>(prm, tb.d_blob, d_counts, grid, st) : launch_eqx<k, MAX_SEATS>(prm, tb.d_blob, d_counts, grid, st)
+    switch (K) {
+        EQX_CASE(0); EQX_CASE(1); EQX_CASE(2); EQX_CASE(3); EQX_CASE(4); EQX_CASE(5);
+        default: return cudaErrorInvalidValue;
+    }
+#undef EQX_CASE
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K5: preflop matrix by brute force over suit-canonical matchups.  A block takes one matchup at a time; its
+// threads split the C(48,5) boards into equal contiguous index ranges (one unranking per thread per matchup).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(HASH_THREADS, 1)
+preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *__restrict__ g_blob,
+                    const CardKey *__restrict__ g_card, long long *__restrict__ wtl) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *slive = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX);
+    __shared__ unsigned long long sred[3];
+    __shared__ CardKey scard[64];
+    stage_blob(H, g_blob);
+    fill_binom(sbin);
+    if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
+    __syncthreads();
+    const uint32_t total = cbinom(48, 5);
+    const uint32_t per = (total + HASH_THREADS - 1) / HASH_THREADS;
+    for (int mi = blockIdx.x; mi < n_mu; mi += gridDim.x) {
+        const Matchup mu = mus[mi];
+        if (threadIdx.x < 3) sred[threadIdx.x] = 0ull;
+        const uint64_t livem = DECK_MASK & ~(mu.hole_a | mu.hole_b);
+        if (threadIdx.x < 64) {
+            const int p = threadIdx.x;
+            if ((livem >> p) & 1ull) slive[__popcll(livem & ((1ull << p) - 1ull))] = live_entry(scard[p], p);
+            if (p >= 48 && p < LIVE_MAX) slive[p] = make_uint4(0, 0, 0, 0);
+        }
+        // the two hands' fixed parts
+        HandState ha{0, 0, (uint32_t)mu.hole_a, (uint32_t)(mu.hole_a >> 32)}, hb{0, 0, (uint32_t)mu.hole_b, (uint32_t)(mu.hole_b >> 32)};
+        {
+            uint64_t x = mu.hole_a;
+            while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; ha.t += scard[p].rk; ha.sn += scard[p].sn; }
+            x = mu.hole_b;
+            while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; hb.t += scard[p].rk; hb.sn += scard[p].sn; }
+        }
+        __syncthreads();
+        const uint32_t lo = per * threadIdx.x, hi = min(total, lo + per);
+        uint32_t wa = 0, wb = 0, tie = 0;
+        if (lo < hi) {
+            Walker<5> w;
+            w.init(lo, 48, sbin, slive, HandState{0, SN_BIAS, 0, 0});
+            for (uint32_t i = lo; i < hi; i++) {
+                const HandState b = w.hand();
+                const uint32_t ka = ht_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, H->D, H->F, H->V);
+                const uint32_t kb = ht_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, H->D, H->F, H->V);
+                wa += ka > kb; wb += kb > ka; tie += ka == kb;
+                w.next(slive, 48);
+            }
+        }
+        const uint32_t sa = warp_sum(wa), sb = warp_sum(wb), stie = warp_sum(tie);
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&sred[0], (unsigned long long)sa); atomicAdd(&sred[1], (unsigned long long)sb);
+            atomicAdd(&sred[2], (unsigned long long)stie);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long *o = reinterpret_cast<unsigned long long *>(wtl);
+            const unsigned long long wgt = (unsigned long long)mu.weight;
+            atomicAdd(&o[3 * mu.cell_ab + 0], wgt * sred[0]);
+            atomicAdd(&o[3 * mu.cell_ab + 1], wgt * sred[2]);
+            atomicAdd(&o[3 * mu.cell_ab + 2], wgt * sred[1]);
+            atomicAdd(&o[3 * mu.cell_ba + 0], wgt * sred[1]);
+            atomicAdd(&o[3 * mu.cell_ba + 1], wgt * sred[2]);
+            atomicAdd(&o[3 * mu.cell_ba + 2], wgt * sred[0]);
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
+                                const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (n_matchups <= 0) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(preflop_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
+    if (e != cudaSuccess) return e;
+    const int grid = n_matchups < di.sm_count ? n_matchups : di.sm_count;
+    preflop_hash_kernel<<<grid, HASH_THREADS, eqx_smem(), st>>>(d_matchups, n_matchups, tb.d_blob, tb.d_card, d_wtl);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K2: all C(52,7) hands in colex order of card ids.  out = hist[9], sum of nibble keys (10 x u64).
+// ---------------------------------------------------------------------------------------------------
+constexpr int ENUM_FOLD = 64;         // hands between folds of the packed 7-bit category counters
+
+__global__ void __launch_bounds__(HASH_THREADS, 1)
+enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
+                  const uint32_t *__restrict__ g_nib, int n_classes, const __grid_constant__ CatBase cb,
+                  unsigned long long *__restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(sdeck + LIVE_MAX);
+    uint32_t *snib = sbin + BIN_N * BIN_K;
+    __shared__ unsigned long long sred[10];
+    __shared__ uint32_t scat[16];
+    stage_blob(H, g_blob);
+    fill_binom(sbin);
+    for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
+    if (threadIdx.x < LIVE_MAX) {
+        const int id = threadIdx.x;                                  // card id 13*suit + rank-2 -> bit position
+        const int p = id + 2 + 3 * (id / 13);
+        sdeck[id] = id < 52 ? live_entry(g_card[p], p) : make_uint4(0, 0, 0, 0);
+    }
+    if (threadIdx.x < 10) { sred[threadIdx.x] = 0ull; scat[threadIdx.x] = cb.v[threadIdx.x]; }
+    __syncthreads();
+
+    uint32_t h[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) h[i] = 0;
+    unsigned long long sumN = 0;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t per = (count + nthreads - 1) / nthreads;
+    const uint64_t me = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t lo = me * per < count ? me * per : count;
+    const uint64_t hi = lo + per < count ? lo + per : count;
+    if (lo < hi) {
+        Walker<7> w;
+        w.init((uint32_t)(first + lo), 52, sbin, sdeck, HandState{0, SN_BIAS, 0, 0});
+        for (uint64_t base = lo; base < hi; base += ENUM_FOLD) {
+            const uint32_t len = (uint32_t)(hi - base < (uint64_t)ENUM_FOLD ? hi - base : (uint64_t)ENUM_FOLD);
+            unsigned long long acc = 0;                               // nine 7-bit counters
+            uint32_t nsum = 0;                                        // <= 64 * 2^24
+            for (uint32_t j = 0; j < len; j++) {
+                const HandState s = w.hand();
+                const uint32_t code = ht_class(s.t, s.sn, s.mlo, s.mhi, H->D, H->F, H->V);
+                const uint32_t cat = code >> 12;
+                acc += 1ull << (7 * cat);
+                nsum += snib[scat[cat] + (code & 0xFFFu)];
+                w.next(sdeck, 52);
+            }
+#pragma unroll
+            for (int i = 0; i < 9; i++) h[i] += (uint32_t)(acc >> (7 * i)) & 127u;
+            sumN += nsum;
+        }
+    }
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const uint32_t s = warp_sum(h[i]);
+        if (lane == 0 && s) atomicAdd(&sred[i], (unsigned long long)s);
+    }
+    sumN = warp_sum64(sumN);
+    if (lane == 0) atomicAdd(&sred[9], sumN);
+    __syncthreads();
+    if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
+}
+
+cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out,
+                              const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (count == 0) return cudaSuccess;
+    const size_t smem = eqx_smem() + (size_t)tb.n_classes * sizeof(uint32_t);
+    cudaError_t e = cudaFuncSetAttribute(enum7_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    uint64_t want = (count + HASH_THREADS - 1) / HASH_THREADS;
+    const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
+    enum7_hash_kernel<<<grid, HASH_THREADS, smem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, tb.cat_base, d_out);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K4: Monte Carlo equity.  One thread per trial (grid-stride).  Deal spec (DESIGN.md "Deal spec v2"):
+// a Fisher-Yates shuffle prefix over the ascending list of live cards, driven by 16-bit Philox fields through
+// Lemire's exact bounded sampler; the thread's deck is a byte array in a bank-private shared-memory column
+// (13 words, stride = blockDim), so every deck access of a warp is conflict-free whatever the indices.
+// Seats are processed in kernel order: random seats first (cards q and q + NR of the deal, the order of
+// deal-hand gameplay.clj:63-75), then the fixed seats; seat_of[] maps back to the caller's seat numbers.
+// ---------------------------------------------------------------------------------------------------
+constexpr int MC_THREADS = 768;
+constexpr int MC_SPARES = 3;
+constexpr uint32_t TAG_DEAL2 = 0x4D434432u;
+
+struct McFyParams {
+    uint32_t h_t[MAX_SEATS], h_sn[MAX_SEATS], h_mlo[MAX_SEATS], h_mhi[MAX_SEATS];   // fixed seats, kernel order
+    HandState base;                           // known community cards, sn biased
+    uint64_t seed, first, count;
+    int n_fixed, n_board, n_live;
+    int seat_of[MAX_SEATS];                   // kernel seat -> caller seat
+    uint32_t deck_init[13];                   // live cards (bit positions, ascending), four per word
+    uint32_t thr[2 * MAX_SEATS + 5];          // ((65536 mod (n_live - i)) << 16) of deal step i
+};
+
+template <int NR> struct McShape {
+    static constexpr int STEPS = 2 * NR + 5;                       // seat cards, then up to 5 community cards
+    static constexpr int BLOCKS = (STEPS + MC_SPARES + 7) / 8;     // Philox blocks (8 16-bit fields each)
+};
+
+// 16-bit field f of the Philox words, moved to the top half of a 32-bit word
+template <int F>
+__device__ __forceinline__ uint32_t field_hi(const uint32_t (&w)[16]) {
+    return (F & 1) ? (w[F >> 1] & 0xFFFF0000u) : (w[F >> 1] << 16);
+}
+
+template <int NR>
+__global__ void __launch_bounds__(MC_THREADS, 1)
+equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__restrict__ g_blob,
+                    const CardKey *__restrict__ g_card, long long *__restrict__ d_counts) {
+    using SH = McShape<NR>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint2 *srep = reinterpret_cast<uint2 *>(smem_raw + sizeof(HashBlob));            // [64 cards][32 lanes]
+    uint32_t *sdeck = reinterpret_cast<uint32_t *>(srep + 64 * 32);                  // [13 words][blockDim]
+    __shared__ unsigned long long sred[19];
+    stage_blob(H, g_blob);
+    for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) { const CardKey k = g_card[i >> 5]; srep[i] = make_uint2(k.rk, k.sn); }
+    if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
+    __syncthreads();
+
+    const int T4 = 4 * (int)blockDim.x;
+    unsigned char *dk = reinterpret_cast<unsigned char *>(sdeck) + 4 * threadIdx.x;
+    const uint2 *rep = srep + (threadIdx.x & 31);
+    const uint32_t k0 = (uint32_t)prm.seed, k1 = (uint32_t)(prm.seed >> 32);
+    const int nl = prm.n_live, nb = prm.n_board, nf = prm.n_fixed;
+    uint32_t acc[MAX_SEATS];                  // per kernel seat: wins << 16 | times at the maximum
+#pragma unroll
+    for (int s = 0; s < MAX_SEATS; s++) acc[s] = 0;
+    uint32_t units = 0;
+
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t tr = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; tr < prm.count; tr += nthreads) {
+        const uint64_t trial = prm.first + tr;
+        uint32_t card[SH::STEPS];
+        for (uint32_t attempt = 0;; attempt++) {
+            uint32_t w[16];
+#pragma unroll
+            for (int b = 0; b < SH::BLOCKS; b++) {
+                uint32_t o[4];
+                philox4x32_10((uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL2, k0, k1, o);
+                w[4 * b] = o[0]; w[4 * b + 1] = o[1]; w[4 * b + 2] = o[2]; w[4 * b + 3] = o[3];
+            }
+#pragma unroll
+            for (int k = 0; k < 13; k++) *reinterpret_cast<uint32_t *>(dk + k * T4) = prm.deck_init[k];
+            bool restart = false;
+            int sp = 0;
+#pragma unroll
+            for (int i = 0; i < SH::STEPS; i++) {
+                if (i >= 2 * NR && i - 2 * NR >= nb) continue;          // community cards already on the table
+                const uint32_t m = (uint32_t)(nl - i);
+                uint32_t r = (i & 1) ? (w[i >> 1] & 0xFFFF0000u) : (w[i >> 1] << 16);
+                uint32_t lo = r * m, hi = __umulhi(r, m);
+                if (lo < prm.thr[i]) {                                   // Lemire rejection zone (p ~ m / 65536): redraw from a spare field
+                    bool ok = false;
+                    while (sp < MC_SPARES && !ok) {
+                        r = sp == 0 ? field_hi<SH::STEPS>(w) : (sp == 1 ? field_hi<SH::STEPS + 1>(w) : field_hi<SH::STEPS + 2>(w));
+                        sp++;
+                        lo = r * m; hi = __umulhi(r, m);
+                        ok = lo >= prm.thr[i];
+                    }
+                    if (!ok) restart = true;
+                }
+                const uint32_t j = (uint32_t)i + hi;
+                unsigned char *pj = dk + (j >> 2) * T4 + (j & 3u);
+                const uint32_t a = *pj;
+                *pj = dk[(i >> 2) * T4 + (i & 3)];
+                card[i] = a;
+            }
+            if (!restart) break;
+        }
+
+        // community cards
+        HandState b = prm.base;
+#pragma unroll
+        for (int k = 0; k < 5; k++) if (k < nb) {
+            const uint32_t a = card[2 * NR + k];
+            const uint2 e = rep[a * 32];
+            b.t += e.x; b.sn += e.y;
+            const uint32_t bit = 1u << (a & 31u);
+            if (a & 32u) b.mhi |= bit; else b.mlo |= bit;
+        }
+        uint32_t key[MAX_SEATS];
+#pragma unroll
+        for (int q = 0; q < NR; q++) {
+            const uint32_t a1 = card[q], a2 = card[q + NR];
+            const uint2 e1 = rep[a1 * 32], e2 = rep[a2 * 32];
+            const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + e1.y + e2.y;
+            if (sn & 0x8888u) {
+                uint32_t mlo = b.mlo, mhi = b.mhi;
+                const uint32_t bit1 = 1u << (a1 & 31u), bit2 = 1u << (a2 & 31u);
+                if (a1 & 32u) mhi |= bit1; else mlo |= bit1;
+                if (a2 & 32u) mhi |= bit2; else mlo |= bit2;
+                key[q] = ht_class(t, sn, mlo, mhi, H->D, H->F, H->V);
+            } else {
+                key[q] = H->V[ht_slot(t, H->D[ht_bucket(t)])];
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS - NR; s++) {
+            key[NR + s] = 0;
+            if (s < nf)
+                key[NR + s] = ht_class(b.t + prm.h_t[s], b.sn + prm.h_sn[s], b.mlo | prm.h_mlo[s], b.mhi | prm.h_mhi[s], H->D, H->F, H->V);
+        }
+        // showdown (gameplay.clj:127-132): sole maximum wins, shared maximum ties
+        uint32_t best = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) best = max(best, key[s]);
+        int nbest = 0;
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) nbest += (key[s] == best);
+        const uint32_t inc = nbest == 1 ? 0x10001u : 1u;
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) { if (key[s] == best) acc[s] += inc; }
+        units++;
+    }
+
+    // per-thread 16-bit halves (the launcher keeps a thread below 65536 trials) -> warp -> block -> global
+    const int lane = threadIdx.x & 31, n_seats = NR + nf;
+#pragma unroll
+    for (int s = 0; s < MAX_SEATS; s++) if (s < n_seats) {
+        const uint32_t w = warp_sum(acc[s] >> 16), e = warp_sum(acc[s] & 0xFFFFu);
+        if (lane == 0) { if (w) atomicAdd(&sred[s], (unsigned long long)w); if (e) atomicAdd(&sred[9 + s], (unsigned long long)e); }
+    }
+    const uint32_t u = warp_sum(units);
+    if (lane == 0 && u) atomicAdd(&sred[18], (unsigned long long)u);
+    __syncthreads();
+    if ((int)threadIdx.x < n_seats) {
+        const int s = threadIdx.x, os = prm.seat_of[s];
+        const unsigned long long w = sred[s], e = sred[9 + s], n = sred[18];
+        unsigned long long *o = reinterpret_cast<unsigned long long *>(d_counts);
+        if (w) atomicAdd(&o[os], w);
+        if (e - w) atomicAdd(&o[9 + os], e - w);
+        if (n - e) atomicAdd(&o[18 + os], n - e);
+    }
+}
+
+static size_t mc_smem() { return sizeof(HashBlob) + 64 * 32 * sizeof(uint2) + 13 * MC_THREADS * sizeof(uint32_t); }
+
+template <int NR>
+static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
+    auto kern = equity_mc_fy_kernel<NR>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mc_smem());
+    if (e != cudaSuccess) return e;
+    kern<<<grid, MC_THREADS, mc_smem(), st>>>(prm, tb.d_blob, tb.d_card, d_counts);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                                long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (n_trials == 0) return cudaSuccess;
+    McFyParams prm;
+    memset(&prm, 0, sizeof prm);
+    uint64_t used = a.board | a.dead;
+    int nr = 0, nf = 0;
+    for (int s = 0; s < a.n_seats; s++) { used |= a.hole[s]; if (!a.hole[s]) nr++; }
+    for (int s = 0, q = 0; s < a.n_seats; s++) {
+        if (!a.hole[s]) { prm.seat_of[q++] = s; continue; }
+        const HandState hs = state_of(a.hole[s], tb.h_card, 0);
+        prm.h_t[nf] = hs.t; prm.h_sn[nf] = hs.sn; prm.h_mlo[nf] = hs.mlo; prm.h_mhi[nf] = hs.mhi;
+        prm.seat_of[nr + nf] = s;
+        nf++;
+    }
+    prm.base = state_of(a.board, tb.h_card, SN_BIAS);
+    prm.seed = seed; prm.n_fixed = nf; prm.n_board = 5 - __builtin_popcountll(a.board);
+    int nl = 0;
+    for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used) >> b) & 1ull) { prm.deck_init[nl >> 2] |= (uint32_t)b << (8 * (nl & 3)); nl++; }
+    prm.n_live = nl;
+    for (int i = 0; i < 2 * MAX_SEATS + 5; i++) { const int m = nl - i; prm.thr[i] = m > 0 ? (uint32_t)(65536 % m) << 16 : 0u; }
+    const int grid = di.sm_count;
+    const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
+    for (uint64_t done = 0; done < n_trials; done += per_launch) {
+        prm.first = first_trial + done;
+        prm.count = (n_trials - done) < per_launch ? (n_trials - done) : per_launch;
+        cudaError_t e;
+        switch (nr) {
+            case 0: e = launch_mc<0>(prm, tb, d_counts, grid, st); break;
+            case 1: e = launch_mc<1>(prm, tb, d_counts, grid, st); break;
+            case 2: e = launch_mc<2>(prm, tb, d_counts, grid, st); break;
+            case 3: e = launch_mc<3>(prm, tb, d_counts, grid, st); break;
+            case 4: e = launch_mc<4>(prm, tb, d_counts, grid, st); break;
+            case 5: e = launch_mc<5>(prm, tb, d_counts, grid, st); break;
+            case 6: e = launch_mc<6>(prm, tb, d_counts, grid, st); break;
+            case 7: e = launch_mc<7>(prm, tb, d_counts, grid, st); break;
+            case 8: e = launch_mc<8>(prm, tb, d_counts, grid, st); break;
+            case 9: e = launch_mc<9>(prm, tb, d_counts, grid, st); break;
+            default: return cudaErrorInvalidValue;
+        }
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+}  // namespace mcp

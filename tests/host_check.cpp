@@ -6,6 +6,7 @@
 #include <cstring>
 #include "../monte-carlo_b200/csrc/eval.cuh"
 #include "../monte-carlo_b200/csrc/eval_tbl.cuh"
+#include "../monte-carlo_b200/csrc/hashtab_build.h"
 #include <vector>
 #include "../oracle/mc_oracle.h"
 
@@ -17,9 +18,44 @@ static int next(int *c, int k, int n) {
     for (int i = 0; i < k; i++) { int lim = (i + 1 < k) ? c[i + 1] : n; if (c[i] + 1 < lim) { c[i]++; for (int j = 0; j < i; j++) c[j] = j; return 1; } }
     return 0;
 }
+// mode 2: the additive-key / perfect-hash evaluator (hashtab.cuh + hashtab_build.h) on every 7-card hand.
+// The representatives are evaluated here with eval.cuh compiled for the host; in the product mc_init does it on the GPU.
+static int check_hash() {
+    static mcp::HashTables T;
+    std::vector<mcp::HashRep> reps;
+    std::string err = "no multiplier tried";
+    for (uint32_t mul : mcp::HT_MUL_CANDIDATES) {
+        mcp::ht_representatives(mul, &reps);
+        std::vector<uint32_t> packed(reps.size());
+        for (size_t i = 0; i < reps.size(); i++) packed[i] = mcp::eval_packed(reps[i].mask);
+        err = mcp::ht_build(reps, packed, mul, &T);
+        if (err.empty()) break;
+    }
+    if (!err.empty()) { fprintf(stderr, "ht_build: %s\n", err.c_str()); return 1; }
+    printf("hash tables: mul=%08x classes=%zu reps=%zu\n", T.mul, T.nib_keys.size(), reps.size());
+    uint64_t total = BINOM[52][7], kbad = 0;
+#pragma omp parallel for reduction(+ : kbad) schedule(static, 1)
+    for (int th = 0; th < 64; th++) {
+        uint64_t chunk = (total + 63) / 64, lo = chunk * th, hi = lo + chunk > total ? total : lo + chunk;
+        if (lo >= hi) continue;
+        int c[7]; unrank(lo, 7, c);
+        for (uint64_t i = lo; i < hi; i++) {
+            uint64_t m = 0; uint32_t t = 0, sn = mcp::SN_BIAS;
+            for (int j = 0; j < 7; j++) { const int p = 16 * (c[j] / 13) + c[j] % 13 + 2; m |= 1ull << p; t += T.card[p].rk; sn += T.card[p].sn; }
+            const uint32_t code = mcp::ht_class(t, sn, (uint32_t)m, (uint32_t)(m >> 32), T.blob.D, T.blob.F, T.blob.V);
+            const uint32_t got = T.nib_keys[T.cat_base[code >> 12] + (code & 0xFFFu)];
+            const uint32_t want = orc_eval_mask(m);
+            if (got != want) { if (kbad < 5) fprintf(stderr, "HASH MISMATCH mask=%016llx want=%06x got=%06x code=%04x\n", (unsigned long long)m, want, got, code); kbad++; }
+            next(c, 7, 52);
+        }
+    }
+    printf("k=7 deck=52 hands=%llu mismatches=%llu (hash evaluator)\n", (unsigned long long)total, (unsigned long long)kbad);
+    return kbad ? 1 : 0;
+}
 int main(int argc, char **argv) {
     int use56 = argc > 1 ? atoi(argv[1]) : 0;     // 1: 56-card deck incl. rank 1 (k = 5 only)
     for (int n = 0; n <= 64; n++) for (int k = 0; k <= 8; k++) BINOM[n][k] = k == 0 ? 1 : (n == 0 ? 0 : BINOM[n - 1][k - 1] + BINOM[n - 1][k]);
+    if (use56 == 2) return check_hash();
     int ncards = use56 ? 56 : 52, per = use56 ? 14 : 13, base = use56 ? 1 : 2;
     uint64_t bad = 0, total_all = 0;
     // the shared-memory table of eval_tbl.cuh, built on the host with the same entry function

@@ -116,7 +116,7 @@ def test_product_evaluator_formulation_on_every_hand(oracle):
     subprocess.check_call(["/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++", "-O2", "-fopenmp", "-o", exe,
                            os.path.join(ROOT, "tests", "host_check.cpp"), "-L" + oracle.ORACLE_DIR, "-loracle",
                            "-Wl,-rpath," + oracle.ORACLE_DIR])
-    for arg in ("0", "1"):
+    for arg in ("0", "1", "2"):       # 2 = the additive-key / perfect-hash evaluator (hashtab.cuh) on all C(52,7) hands
         out = subprocess.run([exe, arg], capture_output=True, text=True)
         assert out.returncode == 0, out.stdout + out.stderr
         assert "mismatches=0" in out.stdout
