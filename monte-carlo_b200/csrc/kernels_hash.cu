@@ -469,7 +469,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
                 *pj = dk[(i >> 2) * T4 + (i & 3)];
                 card[i] = a;
             }
-            if (!restart) break;
+            if (!restart || attempt >= 63u) break;                       // (p(restart) ~ 1e-10; the cap only bounds the loop)
         }
 
         // community cards
