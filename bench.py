@@ -230,7 +230,8 @@ def run_ours(args):
         if not parity:
             raise SystemExit("K1 keys differ from the oracle: refusing to report a number")
     variants = {}
-    for name, fmt in (("packed_key", E.KEY_PACKED), ("nibble_flo", E.KEY_NIBBLE_FLO)):
+    for name, fmt in (("packed_key_bitplane", E.KEY_PACKED), ("nibble_flo_bitplane", E.KEY_NIBBLE_FLO),
+                      ("nibble_rankset_table_v2", E.KEY_NIBBLE_TABLE), ("nibble_hash_v3", E.KEY_NIBBLE_HASH)):
         v_ms = timed_region(torch, dist, world, lambda: k1_step(fmt), max(2, args.steps // 2), 1)
         variants[name] = world * n * max(2, args.steps // 2) / (v_ms * 1e-3)
 
@@ -350,7 +351,7 @@ def run_ours(args):
                        "parallelism": "independent slices per rank, no data-path collective"},
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "eval7_stream_kernel<nibble_table>", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
+                         "kernel": "eval7_stream_hash_kernel", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
                          "int_issue_frac_at_64_ops": (value / world) * OPS["eval"] / int_peak},
             "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
                     "hands_per_step": ne, "call": "mc_eval7_batch (pinned host buffers, 3-stage copy/compute pipeline)"},

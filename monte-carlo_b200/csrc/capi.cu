@@ -110,13 +110,19 @@ int build_tables(DevCtx &c) {
 int upload_tables(DevCtx &c) {
     const HashTables &T = *g_tables;
     const size_t off_card = sizeof(HashBlob), off_nib = off_card + sizeof(T.card);
-    const size_t total = off_nib + T.nib_keys.size() * sizeof(uint32_t);
+    const size_t off_sb = (off_nib + T.nib_keys.size() * sizeof(uint32_t) + 255) & ~(size_t)255;
+    const size_t total = off_sb + SB_BYTES;
+    std::vector<unsigned char> sblob;
+    const std::string err = ht_build_stream_blob(T, &sblob);
+    if (!err.empty()) return fail(MC_ERR_CUDA, "stream blob construction failed: " + err);
     CU(cudaMalloc(&c.d_tables, total));
     unsigned char *base = static_cast<unsigned char *>(c.d_tables);
     CU(cudaMemcpyAsync(base, &T.blob, sizeof(HashBlob), cudaMemcpyHostToDevice, c.stream));
     CU(cudaMemcpyAsync(base + off_card, T.card, sizeof(T.card), cudaMemcpyHostToDevice, c.stream));
     CU(cudaMemcpyAsync(base + off_nib, T.nib_keys.data(), T.nib_keys.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_sb, sblob.data(), SB_BYTES, cudaMemcpyHostToDevice, c.stream));
     CU(cudaStreamSynchronize(c.stream));
+    c.tb.d_stream_blob = base + off_sb;
     c.tb.d_blob = reinterpret_cast<const HashBlob *>(base);
     c.tb.d_card = reinterpret_cast<const CardKey *>(base + off_card);
     c.tb.d_nib = reinterpret_cast<const uint32_t *>(base + off_nib);
@@ -159,10 +165,10 @@ int need_init() {
 }
 
 // context of the calling thread's current device (for the *_dev entry points)
-int current_info(DeviceInfo *out) {
+int current_info(DeviceInfo *out, const DeviceTables **tb = nullptr) {
     int dev = 0;
     CU(cudaGetDevice(&dev));
-    for (auto &c : g_ctx) if (c->device == dev) { *out = c->info; return MC_OK; }
+    for (auto &c : g_ctx) if (c->device == dev) { *out = c->info; if (tb) *tb = &c->tb; return MC_OK; }
     return make_info(dev, out);
 }
 
@@ -172,6 +178,21 @@ int current_tables(DeviceInfo *di, const DeviceTables **tb) {
     CU(cudaGetDevice(&dev));
     for (auto &c : g_ctx) if (c->device == dev) { *di = c->info; *tb = &c->tb; return MC_OK; }
     return fail(MC_ERR_NOT_INIT, "mc_init / mc_init_devices has not been called for the current device");
+}
+
+// K1 dispatch.  key_format: 0 nibble (auto: hash kernel for large aligned batches, else the rank-set-table kernel),
+// 1 packed, 2 nibble via FLO loops, 3 nibble via the rank-set table, 4 nibble via the hash tables (A/B variants)
+constexpr size_t K1_HASH_MIN = (size_t)1 << 21;     // below this the 212 KB table staging per block outweighs the gain
+cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, const DeviceInfo &di,
+                      const DeviceTables *tb, cudaStream_t st) {
+    const bool aligned = ((reinterpret_cast<uintptr_t>(d_masks) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d_keys) & 7) == 0);
+    const bool can_hash = tb && tb->d_stream_blob && aligned;
+    if (key_format == 4 || (key_format == 0 && can_hash && n >= K1_HASH_MIN)) {
+        if (!can_hash) return cudaErrorInvalidValue;
+        return launch_eval7_stream_hash(d_masks, n, d_keys, tb->d_stream_blob, di, st);
+    }
+    const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
+    return launch_eval7_stream(d_masks, n, d_keys, mode, di, st);
 }
 
 int ensure_slots(DevCtx &c) {
@@ -280,11 +301,10 @@ int mc_key_decode(uint32_t key, int32_t *cat, int32_t hit[5], int32_t *n_hit, in
 // ---- K1 --------------------------------------------------------------------------------------------
 int mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream) {
     if (n && (!d_masks || !d_keys)) return fail(MC_ERR_INVALID, "null device buffer");
-    DeviceInfo di;
-    int rc = current_info(&di);
+    DeviceInfo di; const DeviceTables *tb = nullptr;
+    int rc = current_info(&di, &tb);
     if (rc) return rc;
-    const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
-    CU(launch_eval7_stream(d_masks, n, d_keys, mode, di, (cudaStream_t)stream));
+    CU(launch_k1(d_masks, n, d_keys, key_format, di, tb, (cudaStream_t)stream));
     return MC_OK;
 }
 int mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void *stream) {
@@ -296,7 +316,6 @@ int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_
     if (rc) return rc;
     if (n == 0) return MC_OK;
     if (!masks || !keys) return fail(MC_ERR_INVALID, "null buffer");
-    const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
     const int nd = (int)g_ctx.size();
     std::vector<std::unique_lock<std::mutex>> locks;
     for (auto &c : g_ctx) locks.emplace_back(c->mu);
@@ -318,7 +337,7 @@ int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_
             const size_t cnt = std::min(SLOT_HANDS, end[d] - pos[d]);
             CU(cudaSetDevice(c.device));
             CU(cudaMemcpyAsync(c.d_in[s], masks + pos[d], cnt * sizeof(uint64_t), cudaMemcpyHostToDevice, c.slot_stream[s]));
-            CU(launch_eval7_stream(c.d_in[s], cnt, c.d_out[s], mode, c.info, c.slot_stream[s]));
+            CU(launch_k1(c.d_in[s], cnt, c.d_out[s], key_format, c.info, &c.tb, c.slot_stream[s]));
             CU(cudaMemcpyAsync(keys + pos[d], c.d_out[s], cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.slot_stream[s]));
             pos[d] += cnt;
             if (pos[d] < end[d]) more = true;

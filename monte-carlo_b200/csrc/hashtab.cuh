@@ -58,4 +58,22 @@ MCP_HD uint32_t ht_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi,
     return V[ht_slot(t, D[ht_bucket(t)])];
 }
 
+// ---- K1 layout ("stream blob"): everything the streaming kernel needs, in one shared-memory image ------------
+// [0, 64 KB)   256 rows of 256 B, row r = byte value r of the card mask:
+//                  first half   TL[r] replicated for the 32 lanes (bank == lane: conflict-free for any mix of r);
+//                               TL[r] = sum of RKM[rank] over the bits of r read as ranks 0..7 (only r % 4 == 0 occur)
+//                  second half  TH[r] likewise for ranks 8..15 (only r < 128 occur)
+//              the halves that can never be addressed hold the nibble keys (first halves of rows r % 4 != 0, 32 keys
+//              each) and the flush table (second halves of rows r >= 128, 64 u16 each)
+// [64 KB, +16 KB)  D as in HashBlob
+// [80 KB, ...)     V', same slots as HashBlob::V but holding the BYTE ADDRESS (< 65536) of the hand's nibble key
+// so a valid 7-card hand costs 8 conflict-free loads (t), D, V' and the key itself.
+constexpr uint32_t SB_ROWS_BYTES = 65536;
+constexpr uint32_t SB_D_OFF = SB_ROWS_BYTES;
+constexpr uint32_t SB_V_OFF = SB_D_OFF + HT_BUCKETS * 2;
+constexpr uint32_t SB_BYTES = SB_V_OFF + HT_SLOTS * 2;
+static_assert(SB_BYTES % 16 == 0, "stream blob is copied with 16-byte loads");
+MCP_HD uint32_t sb_key_addr(uint32_t dense) { const uint32_t f = dense >> 5; return ((f / 3u) * 4u + f % 3u + 1u) * 256u + (dense & 31u) * 4u; }
+MCP_HD uint32_t sb_flush_addr(uint32_t fi) { return (128u + (fi >> 6)) * 256u + 128u + (fi & 63u) * 2u; }
+
 }  // namespace mcp

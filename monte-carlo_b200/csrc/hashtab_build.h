@@ -120,6 +120,37 @@ inline std::string ht_build(const std::vector<HashRep> &reps, const std::vector<
     return "";
 }
 
+// the shared-memory image of the streaming kernel (layout: hashtab.cuh "K1 layout")
+inline std::string ht_build_stream_blob(const HashTables &T, std::vector<unsigned char> *out) {
+    out->assign(SB_BYTES, 0);
+    unsigned char *B = out->data();
+    auto put32 = [&](uint32_t addr, uint32_t v) { std::memcpy(B + addr, &v, 4); };
+    auto put16 = [&](uint32_t addr, uint16_t v) { std::memcpy(B + addr, &v, 2); };
+    if (T.nib_keys.size() > 192u * 32u) return "too many classes for the key fragments";
+    for (uint32_t r = 0; r < 256; r++) {
+        uint32_t tl = 0, th = 0;
+        for (int k = 0; k < 8; k++) if ((r >> k) & 1u) { tl += T.card[k].rk; th += T.card[8 + k].rk; }
+        for (uint32_t lane = 0; lane < 32; lane++) {
+            if (r % 4 == 0) put32(r * 256 + lane * 4, tl);
+            if (r < 128) put32(r * 256 + 128 + lane * 4, th);
+        }
+    }
+    for (size_t c = 0; c < T.nib_keys.size(); c++) put32(sb_key_addr((uint32_t)c), T.nib_keys[c]);
+    auto addr_of_code = [&](uint16_t code) { return (uint16_t)sb_key_addr(T.cat_base[code >> 12] + (code & 0xFFFu)); };
+    for (uint32_t fi = 0; fi < (uint32_t)HT_FLUSH; fi++) {
+        const int n = __builtin_popcount(fi);
+        if (n >= 5 && n <= 7) put16(sb_flush_addr(fi), addr_of_code(T.blob.F[fi]));
+    }
+    std::memcpy(B + SB_D_OFF, T.blob.D, sizeof T.blob.D);
+    // V': only occupied slots are meaningful; an empty slot keeps address 0 (never read for a valid hand)
+    std::vector<char> occupied(HT_SLOTS, 0);
+    std::vector<HashRep> reps;
+    ht_representatives(T.mul, &reps);
+    for (auto &h : reps) if (h.flush_index == 0xFFFFFFFFu) occupied[ht_slot(h.t, T.blob.D[ht_bucket(h.t)])] = 1;
+    for (uint32_t s = 0; s < (uint32_t)HT_SLOTS; s++) if (occupied[s]) put16(SB_V_OFF + 2 * s, addr_of_code(T.blob.V[s]));
+    return "";
+}
+
 constexpr uint32_t HT_MUL_CANDIDATES[] = {0x165667B1u, 0x27D4EB2Fu, 0x85EBCA6Bu, 0xC2B2AE35u, 0x9E3779B1u};
 
 }  // namespace mcp

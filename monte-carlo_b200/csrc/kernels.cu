@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "eval.cuh"
 #include "eval_tbl.cuh"
+#include "hashtab.cuh"
 #include "philox.cuh"
 
 namespace mcp {
@@ -140,6 +141,85 @@ static cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys
     size_t cap = (size_t)di.sm_count * per_sm;
     int grid = (int)(want < 1 ? 1 : (want > cap ? cap : want));
     kern<<<grid, K1_THREADS, smem, st>>>(d_masks, d_keys, n);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K1 v3: streaming evaluation through the additive-key / perfect-hash tables (hashtab.cuh "K1 layout").
+// A valid 7-card hand of the 52-card deck costs eight conflict-free byte-table loads (one PRMT each builds the
+// address: row = a byte of the mask, column = the lane), the displacement, the slot and the key; the ALU only
+// sums, finds a flush lane and checks validity.  Anything else (5/6 cards, the tests' rank 1, invalid masks)
+// takes the bit-plane evaluator of eval.cuh on a divergent slow path.
+// ---------------------------------------------------------------------------------------------------
+constexpr int K1H_THREADS = 1024;
+
+__device__ __forceinline__ uint32_t k1h_key(uint64_t m, const unsigned char *sb, uint32_t lane4) {
+    const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
+    auto row = [&](uint32_t w, uint32_t sel, uint32_t half) -> uint32_t {
+        return *reinterpret_cast<const uint32_t *>(sb + __byte_perm(w, lane4, sel) + half);
+    };
+    const uint32_t t = (row(lo, 0x5504, 0) + row(lo, 0x5514, 128) + row(lo, 0x5524, 0) + row(lo, 0x5534, 128)) +
+                       (row(hi, 0x5504, 0) + row(hi, 0x5514, 128) + row(hi, 0x5524, 0) + row(hi, 0x5534, 128));
+    // flush lane: only the word holding >= 5 cards can contain it
+    const int p01 = __popc(lo), p23 = __popc(hi);
+    const bool up = p23 >= 5;
+    const uint32_t w = up ? hi : lo;
+    const int pw = up ? p23 : p01;
+    const uint32_t wl = w & 0xFFFFu, wh = w >> 16;
+    const int pl = __popc(wl), ph = pw - pl;
+    const uint32_t fm = pl >= 5 ? wl : (ph >= 5 ? wh : 0u);
+    const uint32_t d = *reinterpret_cast<const uint16_t *>(sb + SB_D_OFF + (t & 0x3FFEu));
+    uint32_t ka = *reinterpret_cast<const uint16_t *>(sb + SB_V_OFF + 2u * ((t >> 16) + d));
+    if (fm) ka = *reinterpret_cast<const uint16_t *>(sb + sb_flush_addr((fm >> 2) & 0x1FFFu));   // masked: an invalid mask must stay inside the table
+    uint32_t key = *reinterpret_cast<const uint32_t *>(sb + ka);
+    const bool deck7 = (p01 + p23 == 7) && (((lo | hi) & 0x80038003u) == 0u);
+    if (!deck7) {
+        const uint32_t n = (uint32_t)(p01 + p23);
+        const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
+        key = ok ? packed_to_nibble(eval_packed(lo, hi)) : 0xFFFFFFFFu;
+    }
+    return key;
+}
+
+__global__ void __launch_bounds__(K1H_THREADS, 1)
+eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, size_t n,
+                         const uint4 *__restrict__ g_blob) {
+    extern __shared__ __align__(16) unsigned char sb[];
+    {
+        uint4 *s = reinterpret_cast<uint4 *>(sb);
+        for (int i = threadIdx.x; i < (int)(SB_BYTES / 16); i += blockDim.x) s[i] = __ldg(g_blob + i);
+    }
+    __syncthreads();
+    const uint32_t lane4 = (threadIdx.x & 31u) * 4u;
+    const size_t npair = n >> 1;
+    const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);
+    uint2 *out = reinterpret_cast<uint2 *>(keys);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npair; i += 2 * stride) {
+        const size_t j = i + stride;
+        const bool two = j < npair;
+        const ulonglong2 a = __ldcs(in + i);
+        ulonglong2 b = make_ulonglong2(0ull, 0ull);
+        if (two) b = __ldcs(in + j);
+        uint2 ka, kb;
+        ka.x = k1h_key(a.x, sb, lane4);
+        ka.y = k1h_key(a.y, sb, lane4);
+        kb.x = k1h_key(b.x, sb, lane4);
+        kb.y = k1h_key(b.y, sb, lane4);
+        __stcs(out + i, ka);
+        if (two) __stcs(out + j, kb);
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) keys[n - 1] = k1h_key(masks[n - 1], sb, lane4);
+}
+
+cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
+                                     const DeviceInfo &di, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(eval7_stream_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_BYTES);
+    if (e != cudaSuccess) return e;
+    size_t want = (n + (size_t)K1H_THREADS * 4 - 1) / ((size_t)K1H_THREADS * 4);
+    const int grid = (int)(want > (size_t)di.sm_count ? (size_t)di.sm_count : want);
+    eval7_stream_hash_kernel<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks, d_keys, n, reinterpret_cast<const uint4 *>(d_stream_blob));
     return cudaGetLastError();
 }
 

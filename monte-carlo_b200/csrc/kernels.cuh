@@ -13,12 +13,16 @@ enum K1Mode : int {
     K1_PACKED = 0,        // packed key, no conversion
     K1_NIBBLE_TABLE = 1,  // nibble key through the shared-memory rank-set table (default)
     K1_NIBBLE_FLO = 2,    // nibble key through FLO/clz loops, no table (A/B variant)
+    K1_NIBBLE_HASH = 3,   // nibble key through the additive-key / perfect-hash tables (large aligned batches)
 };
 
 struct DeviceInfo { int sm_count; int device; };
 
 cudaError_t launch_eval7_stream(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int mode,
                                 const DeviceInfo &di, cudaStream_t st);
+// requires 16-byte aligned masks / 8-byte aligned keys; d_stream_blob = SB_BYTES image (hashtab.cuh "K1 layout")
+cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
+                                     const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,
                                 const DeviceInfo &di, cudaStream_t st);
 // out: 11 x u64 = hist[9], sum of nibble keys (0 unless nib_sum), sum of packed keys; accumulated into
@@ -53,6 +57,7 @@ struct DeviceTables {
     const HashBlob *d_blob = nullptr;        // device: D / F / V
     const CardKey *d_card = nullptr;         // device: 64 entries by bit position
     const uint32_t *d_nib = nullptr;         // device: dense class index -> nibble key
+    const void *d_stream_blob = nullptr;     // device: shared-memory image of the streaming kernel (K1 v3)
     const CardKey *h_card = nullptr;         // host copy of d_card
     CatBase cat_base{};
     uint32_t n_classes = 0;

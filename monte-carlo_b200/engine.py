@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libmcpoker.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 MC_OK, MC_ERR_INVALID, MC_ERR_NOT_INIT, MC_ERR_CUDA, MC_ERR_NO_DEVICE, MC_ERR_TOO_FEW = 0, -1, -2, -3, -4, -5
-KEY_NIBBLE, KEY_PACKED, KEY_NIBBLE_FLO = 0, 1, 2
+KEY_NIBBLE, KEY_PACKED, KEY_NIBBLE_FLO, KEY_NIBBLE_TABLE, KEY_NIBBLE_HASH = 0, 1, 2, 3, 4
 KEY_INVALID = 0xFFFFFFFF
 MAX_SEATS = 9
 N_CLASSES = 169

@@ -33,6 +33,21 @@ static int check_hash() {
     }
     if (!err.empty()) { fprintf(stderr, "ht_build: %s\n", err.c_str()); return 1; }
     printf("hash tables: mul=%08x classes=%zu reps=%zu\n", T.mul, T.nib_keys.size(), reps.size());
+    // the shared-memory image of the streaming kernel (K1 v3), read here exactly as k1h_key reads it for lane 5
+    std::vector<unsigned char> sb;
+    err = mcp::ht_build_stream_blob(T, &sb);
+    if (!err.empty()) { fprintf(stderr, "ht_build_stream_blob: %s\n", err.c_str()); return 1; }
+    auto rd32 = [&](uint32_t a) { uint32_t v; memcpy(&v, sb.data() + a, 4); return v; };
+    auto rd16 = [&](uint32_t a) { uint16_t v; memcpy(&v, sb.data() + a, 2); return (uint32_t)v; };
+    auto stream_key = [&](uint64_t m) -> uint32_t {
+        uint32_t t = 0;
+        for (int b = 0; b < 8; b++) t += rd32((uint32_t)((m >> (8 * b)) & 255u) * 256u + 5 * 4 + (b & 1 ? 128 : 0));
+        uint32_t fm = 0;
+        for (int s4 = 0; s4 < 4; s4++) { uint32_t lane = (uint32_t)(m >> (16 * s4)) & 0xFFFFu; if (__builtin_popcount(lane) >= 5) fm = lane; }
+        uint32_t ka = rd16(mcp::SB_V_OFF + 2u * ((t >> 16) + rd16(mcp::SB_D_OFF + (t & 0x3FFEu))));
+        if (fm) ka = rd16(mcp::sb_flush_addr(fm >> 2));
+        return rd32(ka);
+    };
     uint64_t total = BINOM[52][7], kbad = 0;
 #pragma omp parallel for reduction(+ : kbad) schedule(static, 1)
     for (int th = 0; th < 64; th++) {
@@ -45,6 +60,7 @@ static int check_hash() {
             const uint32_t code = mcp::ht_class(t, sn, (uint32_t)m, (uint32_t)(m >> 32), T.blob.D, T.blob.F, T.blob.V);
             const uint32_t got = T.nib_keys[T.cat_base[code >> 12] + (code & 0xFFFu)];
             const uint32_t want = orc_eval_mask(m);
+            if (stream_key(m) != want) { if (kbad < 5) fprintf(stderr, "STREAM BLOB MISMATCH mask=%016llx\n", (unsigned long long)m); kbad++; }
             if (got != want) { if (kbad < 5) fprintf(stderr, "HASH MISMATCH mask=%016llx want=%06x got=%06x code=%04x\n", (unsigned long long)m, want, got, code); kbad++; }
             next(c, 7, 52);
         }

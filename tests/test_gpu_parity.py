@@ -65,7 +65,7 @@ def test_random_hand_generator_matches_oracle(gpu, oracle):
     assert np.array_equal(gpu.api.random_hands(SEED, 12345, 1000, 5), oracle.random_hands(SEED, 12345, 1000, 5))
 
 
-@pytest.mark.parametrize("fmt", [0, 1, 2], ids=["nibble_table", "packed", "nibble_flo"])
+@pytest.mark.parametrize("fmt", [0, 1, 2, 3, 4], ids=["nibble_auto", "packed", "nibble_flo", "nibble_rankset_table", "nibble_hash"])
 def test_eval7_batch_config1_one_million_hands(gpu, oracle, fmt):
     """BASELINE config 1: 1,000,000 Philox-seeded 7-card hands, 100% equal to the oracle"""
     masks = oracle.random_hands(SEED, 0, 1_000_000)
@@ -100,6 +100,21 @@ def test_eval7_batch_edge_cases(gpu, oracle):
     assert np.array_equal(got, oracle.eval_batch(bad, 0))
 
 
+def test_eval7_batch_hash_kernel_slow_path_and_ragged(gpu, oracle):
+    """K1 v3 (key_format 4): 5/6-card hands, the tests' rank 1 and invalid masks leave the table path; odd sizes"""
+    api = gpu.api
+    base = oracle.random_hands(SEED + 7, 0, 50_001)
+    mixed = np.concatenate([base, oracle.random_hands(SEED, 0, 3000, 5), oracle.random_hands(SEED, 0, 3000, 6),
+                            np.array([oracle.mask_of([(0, 1), (1, 2), (2, 3), (3, 5), (0, 4)]),
+                                      oracle.mask_of([(0, 1), (1, 1), (2, 1), (3, 1), (0, 3)]),
+                                      0, 0b111100, 1 << 0 | 0x7C, 1 << 15 | 0x7C, (1 << 64) - 1, 0xFF << 2,
+                                      0x7F << 2 | 1 << 15, 0x3F << 2 | 1 << 17], dtype=np.uint64)])
+    rng = np.random.default_rng(5)
+    rng.shuffle(mixed)
+    for n in (len(mixed), 4097, 33, 2, 1):
+        assert np.array_equal(api.eval7_batch(mixed[:n], key_format=4), oracle.eval_batch(mixed[:n], 0))
+
+
 def test_eval7_batch_multi_stage_pipeline(gpu, oracle):
     """more hands than one staging buffer holds (4 Mi): exercises the 3-slot H2D/kernel/D2H pipeline"""
     n = (1 << 22) * 2 + 12345
@@ -119,6 +134,7 @@ def test_k1_on_structured_hand_families(gpu, oracle):
         ids = np.array(list(itertools.combinations(rest, 4)), dtype=np.int64)
         masks = np.bitwise_or.reduce(bits[ids], axis=1) | np.bitwise_or.reduce(bits[list(prefix)])
         assert np.array_equal(gpu.api.eval7_batch(masks), oracle.eval_batch(masks, 0))
+        assert np.array_equal(gpu.api.eval7_batch(masks, key_format=4), oracle.eval_batch(masks, 0))
 
 
 # ---- K2: exhaustive enumeration (BASELINE config 2) ---------------------------------------------------

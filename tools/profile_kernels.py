@@ -22,7 +22,7 @@ masks = torch.empty(n, dtype=torch.int64, device="cuda")
 keys = torch.empty(n, dtype=torch.int32, device="cuda")
 E.check(L.mc_random_hands_dev(0x5EED5EED, 0, n, 7, masks.data_ptr(), st))
 for rep in range(2):
-    for fmt in (E.KEY_NIBBLE, E.KEY_PACKED, E.KEY_NIBBLE_FLO):
+    for fmt in (E.KEY_NIBBLE_HASH, E.KEY_NIBBLE_TABLE, E.KEY_PACKED):
         E.check(L.mc_eval7_batch_dev_fmt(masks.data_ptr(), n, keys.data_ptr(), fmt, st))
 out = torch.zeros(16, dtype=torch.int64, device="cuda")
 if which == "k1":
