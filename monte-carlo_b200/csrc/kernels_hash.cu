@@ -374,36 +374,48 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K4: Monte Carlo equity.  One thread per trial (grid-stride).  Deal spec (DESIGN.md "Deal spec v2"):
-// a Fisher-Yates shuffle prefix over the ascending list of live cards, driven by 16-bit Philox fields through
-// Lemire's exact bounded sampler; the thread's deck is a byte array in a bank-private shared-memory column
-// (13 words, stride = blockDim), so every deck access of a warp is conflict-free whatever the indices.
+// K4: Monte Carlo equity.  One thread per trial (grid-stride).  Deal spec v3: the first cards of a
+// Fisher-Yates shuffle of the ascending list of live cards, step i drawing j in [i, n) with Lemire's exact bounded
+// sampler on the 16-bit Philox field i; a trial in which any step falls in the sampler's rejection zone
+// (p ~ 0.5 % per trial) is dealt again from the next Philox attempt.  The thread's deck is a byte array in a
+// bank-private shared-memory column (13 words, stride = blockDim = 512), so every deck access of a warp is
+// conflict-free whatever the indices, and the byte address of position j is (j * 513 & 0x1F803) | 4 * tid.
 // Seats are processed in kernel order: random seats first (cards q and q + NR of the deal, the order of
 // deal-hand gameplay.clj:63-75), then the fixed seats; seat_of[] maps back to the caller's seat numbers.
+// A card's table entry is {premultiplied rank key, suit-counter increment | rank bit << 16}: the low half of the
+// second word counts suits, the high half rebuilds the flush lane without touching the card mask.
 // ---------------------------------------------------------------------------------------------------
-constexpr int MC_THREADS = 768;
-constexpr int MC_SPARES = 3;
-constexpr uint32_t TAG_DEAL2 = 0x4D434432u;
+constexpr int MC_THREADS = 512;
+constexpr int MC_T4 = 4 * MC_THREADS;
+constexpr uint32_t TAG_DEAL3 = 0x4D434433u;
+constexpr int MC_MAX_STEPS = 2 * MAX_SEATS + 5;
 
 struct McFyParams {
     uint32_t h_t[MAX_SEATS], h_sn[MAX_SEATS], h_mlo[MAX_SEATS], h_mhi[MAX_SEATS];   // fixed seats, kernel order
     HandState base;                           // known community cards, sn biased
-    uint64_t seed, first, count;
+    uint64_t first, count;
     int n_fixed, n_board, n_live;
     int seat_of[MAX_SEATS];                   // kernel seat -> caller seat
     uint32_t deck_init[13];                   // live cards (bit positions, ascending), four per word
-    uint32_t thr[2 * MAX_SEATS + 5];          // ((65536 mod (n_live - i)) << 16) of deal step i
+    uint32_t m[MC_MAX_STEPS];                 // n_live - i of deal step i
+    uint32_t thr[MC_MAX_STEPS];               // (65536 mod m[i]) << 16
+    uint32_t rk0[10], rk1[10];                // Philox round keys: seed_lo + r * W0, seed_hi + r * W1
 };
 
 template <int NR> struct McShape {
     static constexpr int STEPS = 2 * NR + 5;                       // seat cards, then up to 5 community cards
-    static constexpr int BLOCKS = (STEPS + MC_SPARES + 7) / 8;     // Philox blocks (8 16-bit fields each)
+    static constexpr int BLOCKS = (STEPS + 7) / 8;                 // Philox blocks (8 16-bit fields each)
 };
 
-// 16-bit field f of the Philox words, moved to the top half of a 32-bit word
-template <int F>
-__device__ __forceinline__ uint32_t field_hi(const uint32_t (&w)[16]) {
-    return (F & 1) ? (w[F >> 1] & 0xFFFF0000u) : (w[F >> 1] << 16);
+__device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const McFyParams &prm,
+                                             uint32_t *o) {
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        const uint64_t p0 = (uint64_t)PHILOX_M0 * c0, p1 = (uint64_t)PHILOX_M1 * c2;
+        c0 = (uint32_t)(p1 >> 32) ^ c1 ^ prm.rk0[r]; c1 = (uint32_t)p1;
+        c2 = (uint32_t)(p0 >> 32) ^ c3 ^ prm.rk1[r]; c3 = (uint32_t)p0;
+    }
+    o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
 }
 
 template <int NR>
@@ -412,20 +424,26 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
                     const CardKey *__restrict__ g_card, long long *__restrict__ d_counts) {
     using SH = McShape<NR>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
-    uint2 *srep = reinterpret_cast<uint2 *>(smem_raw + sizeof(HashBlob));            // [64 cards][32 lanes]
-    uint32_t *sdeck = reinterpret_cast<uint32_t *>(srep + 64 * 32);                  // [13 words][blockDim]
-    __shared__ unsigned long long sred[19];
+    unsigned char *sdeck = smem_raw;                                                         // [13 words][512 threads]
+    uint2 *srep = reinterpret_cast<uint2 *>(smem_raw + 13 * MC_T4);                          // [64 cards][32 lanes]
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw + 13 * MC_T4 + 64 * 32 * sizeof(uint2));
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words
     stage_blob(H, g_blob);
-    for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) { const CardKey k = g_card[i >> 5]; srep[i] = make_uint2(k.rk, k.sn); }
+    for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) {
+        const int p = i >> 5, r = p & 15;
+        const CardKey k = g_card[p];
+        srep[i] = make_uint2(k.rk, k.sn | ((r >= 2 && r <= 14) ? 1u << (16 + r - 2) : 0u));
+    }
     if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
     __syncthreads();
 
-    const int T4 = 4 * (int)blockDim.x;
-    unsigned char *dk = reinterpret_cast<unsigned char *>(sdeck) + 4 * threadIdx.x;
+    const uint32_t tid4 = 4u * threadIdx.x;
+    unsigned char *dk = sdeck + tid4;
     const uint2 *rep = srep + (threadIdx.x & 31);
-    const uint32_t k0 = (uint32_t)prm.seed, k1 = (uint32_t)(prm.seed >> 32);
-    const int nl = prm.n_live, nb = prm.n_board, nf = prm.n_fixed;
+    const int nb = prm.n_board, nf = prm.n_fixed;
+    uint32_t dinit[13];
+#pragma unroll
+    for (int k = 0; k < 13; k++) dinit[k] = prm.deck_init[k];
     uint32_t acc[MAX_SEATS];                  // per kernel seat: wins << 16 | times at the maximum
 #pragma unroll
     for (int s = 0; s < MAX_SEATS; s++) acc[s] = 0;
@@ -436,73 +454,67 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         const uint64_t trial = prm.first + tr;
         uint32_t card[SH::STEPS];
         for (uint32_t attempt = 0;; attempt++) {
-            uint32_t w[16];
+            uint32_t w[4 * SH::BLOCKS];
 #pragma unroll
-            for (int b = 0; b < SH::BLOCKS; b++) {
-                uint32_t o[4];
-                philox4x32_10((uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL2, k0, k1, o);
-                w[4 * b] = o[0]; w[4 * b + 1] = o[1]; w[4 * b + 2] = o[2]; w[4 * b + 3] = o[3];
-            }
+            for (int b = 0; b < SH::BLOCKS; b++)
+                philox_block((uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL3, prm, w + 4 * b);
 #pragma unroll
-            for (int k = 0; k < 13; k++) *reinterpret_cast<uint32_t *>(dk + k * T4) = prm.deck_init[k];
-            bool restart = false;
-            int sp = 0;
+            for (int k = 0; k < 13; k++) *reinterpret_cast<uint32_t *>(dk + k * MC_T4) = dinit[k];
+            bool rej = false;
 #pragma unroll
             for (int i = 0; i < SH::STEPS; i++) {
                 if (i >= 2 * NR && i - 2 * NR >= nb) continue;          // community cards already on the table
-                const uint32_t m = (uint32_t)(nl - i);
-                uint32_t r = (i & 1) ? (w[i >> 1] & 0xFFFF0000u) : (w[i >> 1] << 16);
-                uint32_t lo = r * m, hi = __umulhi(r, m);
-                if (lo < prm.thr[i]) {                                   // Lemire rejection zone (p ~ m / 65536): redraw from a spare field
-                    bool ok = false;
-                    while (sp < MC_SPARES && !ok) {
-                        r = sp == 0 ? field_hi<SH::STEPS>(w) : (sp == 1 ? field_hi<SH::STEPS + 1>(w) : field_hi<SH::STEPS + 2>(w));
-                        sp++;
-                        lo = r * m; hi = __umulhi(r, m);
-                        ok = lo >= prm.thr[i];
-                    }
-                    if (!ok) restart = true;
-                }
-                const uint32_t j = (uint32_t)i + hi;
-                unsigned char *pj = dk + (j >> 2) * T4 + (j & 3u);
+                const uint32_t r = (i & 1) ? (w[i >> 1] & 0xFFFF0000u) : (w[i >> 1] << 16);
+                const uint64_t x = (uint64_t)r * prm.m[i];               // hi = offset in [0, m), lo = Lemire's fraction
+                rej |= (uint32_t)x < prm.thr[i];
+                const uint32_t j513 = (uint32_t)(x >> 32) * 513u + (uint32_t)i * 513u;
+                unsigned char *pj = sdeck + ((j513 & 0x1F803u) | tid4);  // word (j >> 2) of the column, byte j & 3
                 const uint32_t a = *pj;
-                *pj = dk[(i >> 2) * T4 + (i & 3)];
+                *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
                 card[i] = a;
             }
-            if (!restart || attempt >= 63u) break;                       // (p(restart) ~ 1e-10; the cap only bounds the loop)
+            if (!rej || attempt >= 63u) break;                          // (the cap only bounds the loop)
         }
 
-        // community cards
+        // community cards: hand state of the board, and the flush lane of its candidate suit
+        uint2 eb[5];
         HandState b = prm.base;
 #pragma unroll
-        for (int k = 0; k < 5; k++) if (k < nb) {
-            const uint32_t a = card[2 * NR + k];
-            const uint2 e = rep[a * 32];
-            b.t += e.x; b.sn += e.y;
-            const uint32_t bit = 1u << (a & 31u);
-            if (a & 32u) b.mhi |= bit; else b.mlo |= bit;
+        for (int k = 0; k < 5; k++) {
+            eb[k] = make_uint2(0u, 0u);
+            if (k < nb) { eb[k] = rep[card[2 * NR + k] * 32]; b.t += eb[k].x; b.sn += eb[k].y & 0xFFFFu; }
         }
+        // a seat can only flush in a suit the board holds >= 3 of: cbit = that suit's counter bit (0 if none)
+        const uint32_t cbit = ((b.sn + 0x2222u) & 0x8888u) >> 3;
+        const uint32_t blane_w = (cbit & 0x1100u) ? b.mhi : b.mlo;      // known community cards
+        uint32_t lb = cbit ? (((cbit & 0x1010u) ? (blane_w >> 16) : (blane_w & 0xFFFFu)) >> 2) : 0u;
+#pragma unroll
+        for (int k = 0; k < 5; k++) if (k < nb) lb |= (eb[k].y & cbit) ? (eb[k].y >> 16) : 0u;
+
         uint32_t key[MAX_SEATS];
 #pragma unroll
         for (int q = 0; q < NR; q++) {
-            const uint32_t a1 = card[q], a2 = card[q + NR];
-            const uint2 e1 = rep[a1 * 32], e2 = rep[a2 * 32];
-            const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + e1.y + e2.y;
+            const uint2 e1 = rep[card[q] * 32], e2 = rep[card[q + NR] * 32];
+            const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + (e1.y & 0xFFFFu) + (e2.y & 0xFFFFu);
+            uint32_t k = H->V[ht_slot(t, H->D[ht_bucket(t)])];
             if (sn & 0x8888u) {
-                uint32_t mlo = b.mlo, mhi = b.mhi;
-                const uint32_t bit1 = 1u << (a1 & 31u), bit2 = 1u << (a2 & 31u);
-                if (a1 & 32u) mhi |= bit1; else mlo |= bit1;
-                if (a2 & 32u) mhi |= bit2; else mlo |= bit2;
-                key[q] = ht_class(t, sn, mlo, mhi, H->D, H->F, H->V);
-            } else {
-                key[q] = H->V[ht_slot(t, H->D[ht_bucket(t)])];
+                const uint32_t fm = lb | ((e1.y & cbit) ? (e1.y >> 16) : 0u) | ((e2.y & cbit) ? (e2.y >> 16) : 0u);
+                k = H->F[fm];
             }
+            key[q] = k;
         }
 #pragma unroll
         for (int s = 0; s < MAX_SEATS - NR; s++) {
             key[NR + s] = 0;
-            if (s < nf)
-                key[NR + s] = ht_class(b.t + prm.h_t[s], b.sn + prm.h_sn[s], b.mlo | prm.h_mlo[s], b.mhi | prm.h_mhi[s], H->D, H->F, H->V);
+            if (s < nf) {
+                const uint32_t t = b.t + prm.h_t[s], sn = b.sn + prm.h_sn[s];
+                uint32_t k = H->V[ht_slot(t, H->D[ht_bucket(t)])];
+                if (sn & 0x8888u) {
+                    const uint32_t hw = (cbit & 0x1100u) ? prm.h_mhi[s] : prm.h_mlo[s];
+                    k = H->F[lb | (((cbit & 0x1010u) ? (hw >> 16) : (hw & 0xFFFFu)) >> 2)];
+                }
+                key[NR + s] = k;
+            }
         }
         // showdown (gameplay.clj:127-132): sole maximum wins, shared maximum ties
         uint32_t best = 0;
@@ -537,7 +549,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     }
 }
 
-static size_t mc_smem() { return sizeof(HashBlob) + 64 * 32 * sizeof(uint2) + 13 * MC_THREADS * sizeof(uint32_t); }
+static size_t mc_smem() { return 13 * MC_T4 + 64 * 32 * sizeof(uint2) + sizeof(HashBlob) + 19 * sizeof(unsigned long long); }
 
 template <int NR>
 static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
@@ -564,11 +576,12 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
         nf++;
     }
     prm.base = state_of(a.board, tb.h_card, SN_BIAS);
-    prm.seed = seed; prm.n_fixed = nf; prm.n_board = 5 - __builtin_popcountll(a.board);
+    prm.n_fixed = nf; prm.n_board = 5 - __builtin_popcountll(a.board);
+    for (int r = 0; r < 10; r++) { prm.rk0[r] = (uint32_t)seed + (uint32_t)r * PHILOX_W0; prm.rk1[r] = (uint32_t)(seed >> 32) + (uint32_t)r * PHILOX_W1; }
     int nl = 0;
     for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used) >> b) & 1ull) { prm.deck_init[nl >> 2] |= (uint32_t)b << (8 * (nl & 3)); nl++; }
     prm.n_live = nl;
-    for (int i = 0; i < 2 * MAX_SEATS + 5; i++) { const int m = nl - i; prm.thr[i] = m > 0 ? (uint32_t)(65536 % m) << 16 : 0u; }
+    for (int i = 0; i < MC_MAX_STEPS; i++) { const int m = nl - i; prm.m[i] = m > 0 ? (uint32_t)m : 1u; prm.thr[i] = m > 0 ? (uint32_t)(65536 % m) << 16 : 0u; }
     const int grid = di.sm_count;
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
     for (uint64_t done = 0; done < n_trials; done += per_launch) {

@@ -380,18 +380,17 @@ void orc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint
     for (long long i = 0; i < (long long)n; i++) masks[i] = orc_random_hand_mask(seed, first + (uint64_t)i, n_cards);
 }
 
-/* one trial (deal spec v2): random seats (hole mask 0) receive cards in the reference's deal order --
+/* one trial (deal spec v3): random seats (hole mask 0) receive cards in the reference's deal order --
  * one card per random seat, twice round the table (gameplay.clj:63-75) -- then the missing community cards
  * (gameplay.clj:41-54; burns are distributionally irrelevant).  The cards are the first entries of a Fisher-Yates
  * shuffle of the ascending list of live cards:
  *   step i (0-based) draws j uniformly in [i, n) with Lemire's exact bounded sampler on a 16-bit field f:
  *       x = f * (n - i);  rejected iff (x & 0xFFFF) < 65536 mod (n - i);  j = i + (x >> 16)
- *   fields: 16-bit halves (low half first) of the words of Philox blocks 0..B-1, B = ceil((2*nr + 5 + 3) / 8),
- *       block b = Philox4x32-10(key = seed, ctr = (trial_lo, trial_hi, b | attempt << 8, TAG_DEAL2));
+ *   fields: 16-bit halves (low half first) of the words of Philox blocks 0..B-1, B = ceil((2*nr + 5) / 8),
+ *       block b = Philox4x32-10(key = seed, ctr = (trial_lo, trial_hi, b | attempt << 8, TAG_DEAL3));
  *       step i owns field i; seat cards are steps 0..2nr-1, community card k is step 2nr + k
- *   a rejected step redraws from the next of three spare fields (2nr+5, 2nr+6, 2nr+7, shared by the trial);
- *       when none is left the whole trial is dealt again with attempt + 1. */
-#define TAG_DEAL2 0x4D434432u
+ *   if any step of the trial is rejected, the whole trial is dealt again with attempt + 1. */
+#define TAG_DEAL3 0x4D434433u
 int orc_deal_trial(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
                    uint64_t seed, uint64_t trial, uint64_t *holes_out, uint64_t *board_out) {
     uint64_t used = dead_mask | board_mask;
@@ -400,31 +399,25 @@ int orc_deal_trial(const uint64_t *hole_masks, int n_seats, uint64_t board_mask,
     int live[52], n = 0;
     for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used) >> b) & 1ULL) live[n++] = b;
     const int nb = 5 - __builtin_popcountll(board_mask);
-    const int first_spare = 2 * nr + 5, n_blocks = (first_spare + 3 + 7) / 8;
+    const int n_blocks = (2 * nr + 5 + 7) / 8;
     const uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     for (uint32_t attempt = 0;; attempt++) {
         uint32_t field[32];
         for (int b = 0; b < n_blocks; b++) {
-            const uint32_t ctr[4] = {(uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL2};
+            const uint32_t ctr[4] = {(uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL3};
             uint32_t w[4];
             orc_philox4x32_10(ctr, key, w);
             for (int j = 0; j < 4; j++) { field[8 * b + 2 * j] = w[j] & 0xFFFFu; field[8 * b + 2 * j + 1] = w[j] >> 16; }
         }
-        int deck[52], spare = first_spare, failed = 0;
+        int deck[52], rejected = 0;
         for (int i = 0; i < n; i++) deck[i] = live[i];
-        for (int step = 0; step < 2 * nr + nb && !failed; step++) {
-            const int i = step;                               /* deck position == field index == step */
-            const uint32_t m = (uint32_t)(n - i), zone = 65536u % m;
-            uint32_t x = field[i] * m;
-            while ((x & 0xFFFFu) < zone) {
-                if (spare == first_spare + 3) { failed = 1; break; }
-                x = field[spare++] * m;
-            }
-            if (failed) break;
+        for (int i = 0; i < 2 * nr + nb; i++) {               /* deck position == field index == step */
+            const uint32_t m = (uint32_t)(n - i), x = field[i] * m;
+            if ((x & 0xFFFFu) < 65536u % m) { rejected = 1; break; }
             const int j = i + (int)(x >> 16);
             const int c = deck[j]; deck[j] = deck[i]; deck[i] = c;
         }
-        if (failed) continue;
+        if (rejected) continue;
         for (int i = 0; i < 2 * nr; i++) holes_out[rseat[i % nr]] |= 1ULL << deck[i];
         uint64_t bm = board_mask;
         for (int k = 0; k < nb; k++) bm |= 1ULL << deck[2 * nr + k];
