@@ -322,6 +322,35 @@ def run_ours(args):
         "roofline": {"bound": "int_issue", "ops_per_unit": OPS["mc9"], "achieved": rate4 * OPS["mc9"] / 1e12,
                      "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate4 * OPS["mc9"] / (world * int_peak)}}
 
+    # config 5: the 169 x 169 preflop matrix, suit-canonical matchups dealt round-robin over the ranks, one all-reduce
+    if not args.no_matrix:
+        api.preflop_matrix_part(rank, world)                      # warm-up: builds and caches the matchup list
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        part, n_mu = api.preflop_matrix_part(rank, world)
+        mt = torch.from_numpy(part).cuda()
+        if world > 1:
+            dist.all_reduce(mt, op=dist.ReduceOp.SUM)
+        torch.cuda.synchronize()
+        s5 = time.perf_counter() - t0
+        if world > 1:
+            tt = torch.tensor([s5, float(n_mu)], dtype=torch.float64, device="cuda")
+            tmax = tt.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+            s5, n_mu = float(tmax[0].item()), int(tt[1].item())
+        mh = mt.cpu().numpy()
+        aa, kk = api.hole_class(14, 14, False), api.hole_class(13, 13, False)
+        boards5 = n_mu * 1712304
+        work["config5_preflop_matrix"] = {
+            "seconds": s5, "matchups": n_mu, "boards_per_s": boards5 / s5, "evals_per_s": 2 * boards5 / s5,
+            "cell_aa_kk_equals_golden": mh[aa, kk].tolist() == [50371344, 267444, 11004156],
+            "antisymmetric": bool((mh[:, :, 0] == mh[:, :, 2].T).all()),
+            "timing": "wall clock around mc_preflop_matrix_part (host call: upload of the matchup list, K5, download) + all_reduce",
+            "roofline": {"bound": "int_issue", "ops_per_unit": OPS["board2"], "achieved": boards5 / s5 * OPS["board2"] / 1e12,
+                         "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": boards5 / s5 * OPS["board2"] / (world * int_peak)}}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         import oracle_lib as oracle
@@ -377,6 +406,7 @@ def main():
     ap.add_argument("--mc-log2", type=int, default=34)
     ap.add_argument("--mc-budget-s", type=float, default=20.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-matrix", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

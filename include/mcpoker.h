@@ -117,6 +117,9 @@ int  mc_equity_mc_dev(const uint64_t *hole_masks /* host */, int n_seats, uint64
 /* ---- 169 x 169 preflop matrix (K5) -------------------------------------------------------------- */
 /* class id: x = rank-2; pair 13x+x; suited (hi>lo) 13*hi+lo; offsuit 13*lo+hi.  wtl[a][b] = {win,tie,loss} of a */
 int  mc_preflop_matrix(int64_t *wtl /* 169*169*3 */);
+/* share `part` of `n_parts` of the suit-canonical matchup list (one process per GPU: part = rank); the full matrix
+ * is the element-wise sum of the parts (one all-reduce of 169*169*3 int64) */
+int  mc_preflop_matrix_part(int part, int n_parts, int64_t *wtl /* 169*169*3 */, int32_t *n_matchups /* nullable */);
 int  mc_preflop_cells(const int32_t *class_a, const int32_t *class_b, int n_cells, int64_t *wtl /* n*3 */);
 
 #ifdef __cplusplus

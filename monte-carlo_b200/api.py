@@ -126,6 +126,15 @@ def preflop_matrix():
     return out
 
 
+def preflop_matrix_part(part, n_parts):
+    """-> (this part's contribution to the 169x169x3 matrix, number of suit-canonical matchups it covered)"""
+    E.ensure_init()
+    out = np.zeros((E.N_CLASSES, E.N_CLASSES, 3), dtype=np.int64)
+    n = C.c_int32(0)
+    E.check(E.lib().mc_preflop_matrix_part(part, n_parts, out.ctypes.data, C.byref(n)))
+    return out, n.value
+
+
 def hole_class(rank_a, rank_b, suited):
     """169-class id: x = rank-2; pair 13x+x; suited 13*hi+lo; offsuit 13*lo+hi"""
     hi, lo = max(rank_a, rank_b) - 2, min(rank_a, rank_b) - 2

@@ -561,7 +561,16 @@ uint64_t permute_suits(uint64_t m, const int *perm) {
     return r;
 }
 // every unordered pair of disjoint hole-card pairs, folded by the 24 suit permutations
+void build_matchups_uncached(const std::vector<std::pair<int, int>> *only_cells, std::vector<Matchup> *out);
 void build_matchups(const std::vector<std::pair<int, int>> *only_cells, std::vector<Matchup> *out) {
+    if (only_cells) { build_matchups_uncached(only_cells, out); return; }
+    static std::mutex mu;
+    static std::vector<Matchup> all;                 // the full list never changes: build it once per process
+    std::lock_guard<std::mutex> lk(mu);
+    if (all.empty()) build_matchups_uncached(nullptr, &all);
+    *out = all;
+}
+void build_matchups_uncached(const std::vector<std::pair<int, int>> *only_cells, std::vector<Matchup> *out) {
     std::vector<uint64_t> holes;
     for (int a = 0; a < 52; a++) for (int b = a + 1; b < 52; b++) holes.push_back(mc_card_bit(a) | mc_card_bit(b));
     int perms[24][4], np = 0;
@@ -639,6 +648,18 @@ int mc_preflop_matrix(int64_t *wtl) {
     int rc = run_matchups(mus, &full);
     if (rc) return rc;
     for (size_t i = 0; i < full.size(); i++) wtl[i] = full[i];
+    return MC_OK;
+}
+int mc_preflop_matrix_part(int part, int n_parts, int64_t *wtl, int32_t *n_matchups) {
+    if (!wtl || n_parts < 1 || part < 0 || part >= n_parts) return fail(MC_ERR_INVALID, "bad part / n_parts");
+    std::vector<Matchup> all, mine;
+    build_matchups(nullptr, &all);
+    for (size_t i = (size_t)part; i < all.size(); i += (size_t)n_parts) mine.push_back(all[i]);
+    std::vector<long long> full;
+    int rc = run_matchups(mine, &full);
+    if (rc) return rc;
+    for (size_t i = 0; i < full.size(); i++) wtl[i] = full[i];
+    if (n_matchups) *n_matchups = (int32_t)mine.size();
     return MC_OK;
 }
 int mc_preflop_cells(const int32_t *class_a, const int32_t *class_b, int n_cells, int64_t *wtl) {

@@ -296,19 +296,20 @@ cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long 
 // ---------------------------------------------------------------------------------------------------
 // K2: all C(52,7) hands in colex order of card ids.  out = hist[9], sum of nibble keys (10 x u64).
 // ---------------------------------------------------------------------------------------------------
-constexpr int ENUM_FOLD = 64;         // hands between folds of the packed 7-bit category counters
+constexpr int ENUM_FOLD = 32;         // hands between folds of the packed category counters (6-bit fields hold <= 32... 63)
+constexpr int ENUM_THREADS = 1024;
 
-__global__ void __launch_bounds__(HASH_THREADS, 1)
+__global__ void __launch_bounds__(ENUM_THREADS, 1)
 enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
                   const uint32_t *__restrict__ g_nib, int n_classes, const __grid_constant__ CatBase cb,
                   unsigned long long *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
     uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
-    uint32_t *sbin = reinterpret_cast<uint32_t *>(sdeck + LIVE_MAX);
+    uint4 *scat = sdeck + LIVE_MAX;                                   // 16 entries: {dense base, counter increments lo / hi, 0}
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(scat + 16);   // 16 words
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
     uint32_t *snib = sbin + BIN_N * BIN_K;
-    __shared__ unsigned long long sred[10];
-    __shared__ uint32_t scat[16];
     stage_blob(H, g_blob);
     fill_binom(sbin);
     for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
@@ -317,7 +318,11 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
         const int p = id + 2 + 3 * (id / 13);
         sdeck[id] = id < 52 ? live_entry(g_card[p], p) : make_uint4(0, 0, 0, 0);
     }
-    if (threadIdx.x < 10) { sred[threadIdx.x] = 0ull; scat[threadIdx.x] = cb.v[threadIdx.x]; }
+    if (threadIdx.x < 16) {
+        const int c = threadIdx.x;                                   // categories 0..3: 8-bit fields of lo; 4..8: 6-bit fields of hi
+        sred[c] = 0ull;
+        scat[c] = make_uint4(c < 10 ? cb.v[c] : 0u, c < 4 ? 1u << (8 * c) : 0u, (c >= 4 && c < 9) ? 1u << (6 * (c - 4)) : 0u, 0u);
+    }
     __syncthreads();
 
     uint32_t h[9];
@@ -334,18 +339,19 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
         w.init((uint32_t)(first + lo), 52, sbin, sdeck, HandState{0, SN_BIAS, 0, 0});
         for (uint64_t base = lo; base < hi; base += ENUM_FOLD) {
             const uint32_t len = (uint32_t)(hi - base < (uint64_t)ENUM_FOLD ? hi - base : (uint64_t)ENUM_FOLD);
-            unsigned long long acc = 0;                               // nine 7-bit counters
-            uint32_t nsum = 0;                                        // <= 64 * 2^24
+            uint32_t acc_lo = 0, acc_hi = 0, nsum = 0;                // nsum <= 32 * 2^24
             for (uint32_t j = 0; j < len; j++) {
                 const HandState s = w.hand();
                 const uint32_t code = ht_class(s.t, s.sn, s.mlo, s.mhi, H->D, H->F, H->V);
-                const uint32_t cat = code >> 12;
-                acc += 1ull << (7 * cat);
-                nsum += snib[scat[cat] + (code & 0xFFFu)];
+                const uint4 ci = scat[code >> 12];
+                acc_lo += ci.y; acc_hi += ci.z;
+                nsum += snib[ci.x + (code & 0xFFFu)];
                 w.next(sdeck, 52);
             }
 #pragma unroll
-            for (int i = 0; i < 9; i++) h[i] += (uint32_t)(acc >> (7 * i)) & 127u;
+            for (int i = 0; i < 4; i++) h[i] += (acc_lo >> (8 * i)) & 255u;
+#pragma unroll
+            for (int i = 4; i < 9; i++) h[i] += (acc_hi >> (6 * (i - 4))) & 63u;
             sumN += nsum;
         }
     }
@@ -361,15 +367,20 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
     if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
 }
 
+static size_t enum_smem(int n_classes) {
+    return sizeof(HashBlob) + (LIVE_MAX + 16) * sizeof(uint4) + 16 * sizeof(unsigned long long) +
+           (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
+}
+
 cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out,
                               const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (count == 0) return cudaSuccess;
-    const size_t smem = eqx_smem() + (size_t)tb.n_classes * sizeof(uint32_t);
+    const size_t smem = enum_smem((int)tb.n_classes);
     cudaError_t e = cudaFuncSetAttribute(enum7_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    uint64_t want = (count + HASH_THREADS - 1) / HASH_THREADS;
+    uint64_t want = (count + ENUM_THREADS - 1) / ENUM_THREADS;
     const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
-    enum7_hash_kernel<<<grid, HASH_THREADS, smem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, tb.cat_base, d_out);
+    enum7_hash_kernel<<<grid, ENUM_THREADS, smem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, tb.cat_base, d_out);
     return cudaGetLastError();
 }
 
@@ -482,7 +493,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 #pragma unroll
         for (int k = 0; k < 5; k++) {
             eb[k] = make_uint2(0u, 0u);
-            if (k < nb) { eb[k] = rep[card[2 * NR + k] * 32]; b.t += eb[k].x; b.sn += eb[k].y & 0xFFFFu; }
+            if (k < nb) { eb[k] = rep[card[2 * NR + k] * 32]; b.t += eb[k].x; b.sn += eb[k].y; }      // (high half of the sum is never read)
         }
         // a seat can only flush in a suit the board holds >= 3 of: cbit = that suit's counter bit (0 if none)
         const uint32_t cbit = ((b.sn + 0x2222u) & 0x8888u) >> 3;
@@ -495,7 +506,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 #pragma unroll
         for (int q = 0; q < NR; q++) {
             const uint2 e1 = rep[card[q] * 32], e2 = rep[card[q + NR] * 32];
-            const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + (e1.y & 0xFFFFu) + (e2.y & 0xFFFFu);
+            const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + e1.y + e2.y;
             uint32_t k = H->V[ht_slot(t, H->D[ht_bucket(t)])];
             if (sn & 0x8888u) {
                 const uint32_t fm = lb | ((e1.y & cbit) ? (e1.y >> 16) : 0u) | ((e2.y & cbit) ? (e2.y >> 16) : 0u);

@@ -300,3 +300,22 @@ def test_preflop_cells(gpu, oracle):
     wtl = (C.c_int64 * 3)()
     assert oracle.lib().orc_preflop_cell(cells[3][0], cells[3][1], 0, wtl) == 0
     assert got[3].tolist() == list(wtl)
+
+
+def test_preflop_matrix_full_properties(gpu):
+    """BASELINE config 5: the whole 169 x 169 matrix by exhaustive boards; checked through the golden AA-KK cell,
+    antisymmetry, row totals, and additivity of the per-rank parts (SURVEY 8d cfg 5)."""
+    api = gpu.api
+    m = api.preflop_matrix()
+    aa, kk = api.hole_class(14, 14, False), api.hole_class(13, 13, False)
+    assert m[aa, kk].tolist() == [50371344, 267444, 11004156]          # win, tie, loss of AA
+    assert np.array_equal(m[:, :, 0], m[:, :, 2].T) and np.array_equal(m[:, :, 1], m[:, :, 1].T)
+    boards = 1712304
+    for cls in range(169):
+        a, b = divmod(cls, 13)
+        combos = 6 if a == b else (4 if a > b else 12)
+        assert int(m[cls].sum()) == combos * 1225 * boards             # C(50,2) opposing holes x C(48,5) boards
+    p0, n0 = api.preflop_matrix_part(0, 3)
+    p1, n1 = api.preflop_matrix_part(1, 3)
+    p2, n2 = api.preflop_matrix_part(2, 3)
+    assert np.array_equal(p0 + p1 + p2, m) and n0 + n1 + n2 > 40000
