@@ -25,29 +25,18 @@ cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t
                                      const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,
                                 const DeviceInfo &di, cudaStream_t st);
-// out: 11 x u64 = hist[9], sum of nibble keys (0 unless nib_sum), sum of packed keys; accumulated into
-cudaError_t launch_enum7(uint64_t first, uint64_t count, unsigned long long *d_out, bool nib_sum,
-                         const DeviceInfo &di, cudaStream_t st);
-
 struct EquityArgs {
     uint64_t hole[MAX_SEATS];   // 0 = random seat (Monte Carlo only)
     uint64_t board;             // known community cards
     uint64_t dead;
     int n_seats;
 };
-// d_counts: 27 x int64 = win[9] tie[9] loss[9]; accumulated into
-cudaError_t launch_equity_exhaustive(const EquityArgs &a, uint64_t first_board, uint64_t n_boards,
-                                     long long *d_counts, const DeviceInfo &di, cudaStream_t st);
-cudaError_t launch_equity_mc(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
-                             long long *d_counts, const DeviceInfo &di, cudaStream_t st);
 // one warp: keys per seat, winner bitmask, tie-group index per seat, number of groups
 // d_out: uint32 keys[9], uint32 winners, int32 group_of[9], int32 n_groups  (20 words)
 cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, cudaStream_t st);
 
 // preflop matrix: matchup list = (hole_a, hole_b, cell index, weight); each block takes matchups
 struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weight; };
-cudaError_t launch_preflop(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
-                           const DeviceInfo &di, cudaStream_t st);
 
 // ---- kernels on the additive-key / perfect-hash evaluator (kernels_hash.cu, hashtab.cuh) ----------------
 struct HashBlob;
