@@ -40,6 +40,40 @@ __device__ __forceinline__ void colex_unrank(uint32_t idx, int n, const uint32_t
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Table staging by the TMA engine: one elected thread arms an mbarrier with the byte count and issues 1-D bulk
+// copies global -> shared (cp.async.bulk, SASS UBLKCP); the other threads keep filling the small per-block tables
+// and everybody waits on the barrier's phase 0.  bytes % 16 == 0, dst and src 16-byte aligned.
+// ---------------------------------------------------------------------------------------------------
+struct BulkStage {
+    uint32_t bar;
+    __device__ __forceinline__ void start(unsigned long long *mbar, void *smem_dst, const void *gsrc, uint32_t bytes) {
+        bar = (uint32_t)__cvta_generic_to_shared(mbar);
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");          // the async proxy sees the initialised barrier
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(smem_dst);
+            const char *src = static_cast<const char *>(gsrc);
+            constexpr uint32_t CHUNK = 32768;
+            for (uint32_t off = 0; off < bytes; off += CHUNK) {
+                const uint32_t n = bytes - off < CHUNK ? bytes - off : CHUNK;
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(dst + off), "l"(src + off), "r"(n), "r"(bar) : "memory");
+            }
+        }
+    }
+    // every thread of the block; includes the block-wide barrier that publishes the other threads' table fills
+    __device__ __forceinline__ void wait() {
+        __syncthreads();                      // the mbarrier is initialised and armed before anybody polls it
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}"
+                         : "=r"(done) : "r"(bar) : "memory");
+    }
+};
+
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
 #pragma unroll

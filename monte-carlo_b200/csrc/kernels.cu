@@ -146,11 +146,10 @@ __global__ void __launch_bounds__(K1H_THREADS, 1)
 eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, size_t n,
                          const uint4 *__restrict__ g_blob) {
     extern __shared__ __align__(16) unsigned char sb[];
-    {
-        uint4 *s = reinterpret_cast<uint4 *>(sb);
-        for (int i = threadIdx.x; i < (int)(SB_BYTES / 16); i += blockDim.x) s[i] = __ldg(g_blob + i);
-    }
-    __syncthreads();
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, sb, g_blob, SB_BYTES);
+    stage.wait();
     const uint32_t lane4 = (threadIdx.x & 31u) * 4u;
     const size_t npair = n >> 1;
     const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);

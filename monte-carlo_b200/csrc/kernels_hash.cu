@@ -23,13 +23,6 @@ __host__ __device__ __forceinline__ uint4 live_entry(const CardKey &k, int pos) 
     return make_uint4(k.rk, k.sn, pos < 32 ? 1u << pos : 0u, pos >= 32 ? 1u << (pos - 32) : 0u);
 }
 
-// stage the hash blob in shared memory (16-byte loads; the blob stays L2-resident across blocks)
-__device__ __forceinline__ void stage_blob(HashBlob *dst, const HashBlob *__restrict__ src) {
-    const uint4 *g = reinterpret_cast<const uint4 *>(src);
-    uint4 *s = reinterpret_cast<uint4 *>(dst);
-    for (int i = threadIdx.x; i < (int)(sizeof(HashBlob) / 16); i += blockDim.x) s[i] = __ldg(g + i);
-}
-
 // Walks K-subsets of the live list in colex order, keeping the partial hands P[i] = base + cards c[i..K-1] in
 // registers: the common step (lowest card moves) costs one 16-byte shared load and four integer ops.
 template <int K>
@@ -131,11 +124,13 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
     uint4 *slive = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
     uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX);
     __shared__ unsigned long long sred[19];
-    stage_blob(H, g_blob);
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
     if (threadIdx.x < LIVE_MAX) slive[threadIdx.x] = prm.live[threadIdx.x];
     if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
-    __syncthreads();
+    stage.wait();
 
     const int n_seats = prm.n_seats, nl = prm.n_live;
     Tally<NS> tl; tl.clear();
@@ -226,10 +221,12 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
     uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX);
     __shared__ unsigned long long sred[3];
     __shared__ CardKey scard[64];
-    stage_blob(H, g_blob);
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
     if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
-    __syncthreads();
+    stage.wait();
     const uint32_t total = cbinom(48, 5);
     const uint32_t per = (total + HASH_THREADS - 1) / HASH_THREADS;
     for (int mi = blockIdx.x; mi < n_mu; mi += gridDim.x) {
@@ -310,7 +307,9 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
     unsigned long long *sred = reinterpret_cast<unsigned long long *>(scat + 16);   // 16 words
     uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
     uint32_t *snib = sbin + BIN_N * BIN_K;
-    stage_blob(H, g_blob);
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
     for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
     if (threadIdx.x < LIVE_MAX) {
@@ -323,7 +322,7 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
         sred[c] = 0ull;
         scat[c] = make_uint4(c < 10 ? cb.v[c] : 0u, c < 4 ? 1u << (8 * c) : 0u, (c >= 4 && c < 9) ? 1u << (6 * (c - 4)) : 0u, 0u);
     }
-    __syncthreads();
+    stage.wait();
 
     uint32_t h[9];
 #pragma unroll
@@ -438,15 +437,16 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     unsigned char *sdeck = smem_raw;                                                         // [13 words][512 threads]
     uint2 *srep = reinterpret_cast<uint2 *>(smem_raw + 13 * MC_T4);                          // [64 cards][32 lanes]
     HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw + 13 * MC_T4 + 64 * 32 * sizeof(uint2));
-    unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words
-    stage_blob(H, g_blob);
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words + the mbarrier
+    BulkStage stage;
+    stage.start(sred + 19, H, g_blob, (uint32_t)sizeof(HashBlob));
     for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) {
         const int p = i >> 5, r = p & 15;
         const CardKey k = g_card[p];
         srep[i] = make_uint2(k.rk, k.sn | ((r >= 2 && r <= 14) ? 1u << (16 + r - 2) : 0u));
     }
     if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
-    __syncthreads();
+    stage.wait();
 
     const uint32_t tid4 = 4u * threadIdx.x;
     unsigned char *dk = sdeck + tid4;
@@ -560,7 +560,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     }
 }
 
-static size_t mc_smem() { return 13 * MC_T4 + 64 * 32 * sizeof(uint2) + sizeof(HashBlob) + 19 * sizeof(unsigned long long); }
+static size_t mc_smem() { return 13 * MC_T4 + 64 * 32 * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
 
 template <int NR>
 static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
