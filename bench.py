@@ -51,7 +51,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "25"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -209,13 +209,21 @@ def run_ours(args):
         launches[0] += 1
 
     sampler = ClockSampler(local)
+    sampler.start()                              # nvidia-smi needs ~0.1 s to deliver its first sample
     for _ in range(args.warmup):
         k1_step()
-    sampler.start()
     launches[0] = 0
     ms = timed_region(torch, dist, world, k1_step, args.steps, 0)
-    clocks = sampler.stop()
     gpu_launches = launches[0]
+    # the timed region lasts tens of milliseconds: keep the SAME launches going (untimed, uncounted) for 0.5 s so that
+    # the clock / throttle samples are taken under the load that was just timed
+    sampler.rows.clear()
+    t_probe = time.perf_counter()
+    while time.perf_counter() - t_probe < 0.5:
+        k1_step()
+        torch.cuda.synchronize()
+    clocks = sampler.stop()
+    clocks["window"] = "0.5 s of the same K1 launches issued right after the timed region (the region itself is %.0f ms)" % ms
     value = world * n * args.steps / (ms * 1e-3)
     per_launch_ms = ms / args.steps
     achieved_gbs = n * ALGO_BYTES_PER_EVAL / (per_launch_ms * 1e-3) / 1e9
