@@ -384,10 +384,11 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K4: Monte Carlo equity.  One thread per trial (grid-stride).  Deal spec v3: the first cards of a
-// Fisher-Yates shuffle of the ascending list of live cards, step i drawing j in [i, n) with Lemire's exact bounded
-// sampler on the 16-bit Philox field i; a trial in which any step falls in the sampler's rejection zone
-// (p ~ 0.5 % per trial) is dealt again from the next Philox attempt.  The thread's deck is a byte array in a
+// K4: Monte Carlo equity.  One thread per trial (grid-stride).  Deal spec v4: the first cards of a
+// Fisher-Yates shuffle of the ascending list of live cards.  One 32-bit Philox word serves three consecutive
+// steps by a multiply chain (x = r * m: the high word is the draw, the low word is the next r), which equals
+// Lemire's exact bounded sampler on the product of the three ranges; a trial in which a word ends in the
+// sampler's rejection zone (p ~ 2e-4 per trial) is dealt again from the next Philox attempt.  The thread's deck is a byte array in a
 // bank-private shared-memory column (13 words, stride = blockDim = 512), so every deck access of a warp is
 // conflict-free whatever the indices, and the byte address of position j is (j * 513 & 0x1F803) | 4 * tid.
 // Seats are processed in kernel order: random seats first (cards q and q + NR of the deal, the order of
@@ -397,7 +398,7 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
 // ---------------------------------------------------------------------------------------------------
 constexpr int MC_THREADS = 512;
 constexpr int MC_T4 = 4 * MC_THREADS;
-constexpr uint32_t TAG_DEAL3 = 0x4D434433u;
+constexpr uint32_t TAG_DEAL4 = 0x4D434434u;
 constexpr int MC_MAX_STEPS = 2 * MAX_SEATS + 5;
 
 struct McFyParams {
@@ -408,13 +409,14 @@ struct McFyParams {
     int seat_of[MAX_SEATS];                   // kernel seat -> caller seat
     uint32_t deck_init[13];                   // live cards (bit positions, ascending), four per word
     uint32_t m[MC_MAX_STEPS];                 // n_live - i of deal step i
-    uint32_t thr[MC_MAX_STEPS];               // (65536 mod m[i]) << 16
+    uint32_t thr[(MC_MAX_STEPS + 2) / 3];     // 2^32 mod (product of the m[i] of the steps word w serves)
     uint32_t rk0[10], rk1[10];                // Philox round keys: seed_lo + r * W0, seed_hi + r * W1
 };
 
 template <int NR> struct McShape {
     static constexpr int STEPS = 2 * NR + 5;                       // seat cards, then up to 5 community cards
-    static constexpr int BLOCKS = (STEPS + 7) / 8;                 // Philox blocks (8 16-bit fields each)
+    static constexpr int WORDS = (STEPS + 2) / 3;                  // one 32-bit Philox word per three steps
+    static constexpr int BLOCKS = (WORDS + 3) / 4;
 };
 
 __device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const McFyParams &prm,
@@ -468,21 +470,24 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
             uint32_t w[4 * SH::BLOCKS];
 #pragma unroll
             for (int b = 0; b < SH::BLOCKS; b++)
-                philox_block((uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL3, prm, w + 4 * b);
+                philox_block((uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL4, prm, w + 4 * b);
 #pragma unroll
             for (int k = 0; k < 13; k++) *reinterpret_cast<uint32_t *>(dk + k * MC_T4) = dinit[k];
             bool rej = false;
+            uint32_t r = 0;
 #pragma unroll
             for (int i = 0; i < SH::STEPS; i++) {
-                if (i >= 2 * NR && i - 2 * NR >= nb) continue;          // community cards already on the table
-                const uint32_t r = (i & 1) ? (w[i >> 1] & 0xFFFF0000u) : (w[i >> 1] << 16);
-                const uint64_t x = (uint64_t)r * prm.m[i];               // hi = offset in [0, m), lo = Lemire's fraction
-                rej |= (uint32_t)x < prm.thr[i];
-                const uint32_t j513 = (uint32_t)(x >> 32) * 513u + (uint32_t)i * 513u;
-                unsigned char *pj = sdeck + ((j513 & 0x1F803u) | tid4);  // word (j >> 2) of the column, byte j & 3
-                const uint32_t a = *pj;
-                *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
-                card[i] = a;
+                if (i % 3 == 0) r = w[i / 3];
+                if (i < 2 * NR || i - 2 * NR < nb) {                     // (else: community card already on the table)
+                    const uint64_t x = (uint64_t)r * prm.m[i];           // hi = offset in [0, m), lo = the next r
+                    r = (uint32_t)x;
+                    const uint32_t j513 = (uint32_t)(x >> 32) * 513u + (uint32_t)i * 513u;
+                    unsigned char *pj = sdeck + ((j513 & 0x1F803u) | tid4);   // word (j >> 2) of the column, byte j & 3
+                    const uint32_t a = *pj;
+                    *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
+                    card[i] = a;
+                }
+                if (i % 3 == 2 || i == SH::STEPS - 1) rej |= r < prm.thr[i / 3];   // Lemire's zone of the word's product
             }
             if (!rej || attempt >= 63u) break;                          // (the cap only bounds the loop)
         }
@@ -592,7 +597,13 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
     int nl = 0;
     for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used) >> b) & 1ull) { prm.deck_init[nl >> 2] |= (uint32_t)b << (8 * (nl & 3)); nl++; }
     prm.n_live = nl;
-    for (int i = 0; i < MC_MAX_STEPS; i++) { const int m = nl - i; prm.m[i] = m > 0 ? (uint32_t)m : 1u; prm.thr[i] = m > 0 ? (uint32_t)(65536 % m) << 16 : 0u; }
+    for (int i = 0; i < MC_MAX_STEPS; i++) { const int m = nl - i; prm.m[i] = m > 0 ? (uint32_t)m : 1u; }
+    for (int w = 0; w < (MC_MAX_STEPS + 2) / 3; w++) {
+        uint64_t prod = 1;
+        for (int i = 3 * w; i < 3 * w + 3 && i < 2 * nr + 5; i++)
+            if (i < 2 * nr || i - 2 * nr < prm.n_board) prod *= prm.m[i];
+        prm.thr[w] = (uint32_t)((1ull << 32) % prod);
+    }
     const int grid = di.sm_count;
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
     for (uint64_t done = 0; done < n_trials; done += per_launch) {

@@ -380,17 +380,18 @@ void orc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint
     for (long long i = 0; i < (long long)n; i++) masks[i] = orc_random_hand_mask(seed, first + (uint64_t)i, n_cards);
 }
 
-/* one trial (deal spec v3): random seats (hole mask 0) receive cards in the reference's deal order --
+/* one trial (deal spec v4): random seats (hole mask 0) receive cards in the reference's deal order --
  * one card per random seat, twice round the table (gameplay.clj:63-75) -- then the missing community cards
  * (gameplay.clj:41-54; burns are distributionally irrelevant).  The cards are the first entries of a Fisher-Yates
- * shuffle of the ascending list of live cards:
- *   step i (0-based) draws j uniformly in [i, n) with Lemire's exact bounded sampler on a 16-bit field f:
- *       x = f * (n - i);  rejected iff (x & 0xFFFF) < 65536 mod (n - i);  j = i + (x >> 16)
- *   fields: 16-bit halves (low half first) of the words of Philox blocks 0..B-1, B = ceil((2*nr + 5) / 8),
- *       block b = Philox4x32-10(key = seed, ctr = (trial_lo, trial_hi, b | attempt << 8, TAG_DEAL3));
- *       step i owns field i; seat cards are steps 0..2nr-1, community card k is step 2nr + k
- *   if any step of the trial is rejected, the whole trial is dealt again with attempt + 1. */
-#define TAG_DEAL3 0x4D434433u
+ * shuffle of the ascending list of live cards; seat cards are steps 0..2nr-1, community card k is step 2nr + k
+ * (steps of community cards that are already known are skipped), step i swaps deck[i] with deck[j], j in [i, n):
+ *   word w (the w-th 32-bit output of Philox blocks 0..B-1, block b = Philox4x32-10(key = seed,
+ *   ctr = (trial_lo, trial_hi, b | attempt << 8, TAG_DEAL4))) serves steps 3w, 3w+1, 3w+2 by a multiply chain:
+ *       r = word;  for each of its steps:  x = r * (n - i);  j = i + (x >> 32);  r = x & 0xFFFFFFFF
+ *   which is floor(word * M / 2^32) in mixed radix, M = product of the (n - i) of its executed steps, so by Lemire's
+ *   bounded sampler it is exact iff the final r >= 2^32 mod M; otherwise the whole trial is dealt again with
+ *   attempt + 1. */
+#define TAG_DEAL4 0x4D434434u
 int orc_deal_trial(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
                    uint64_t seed, uint64_t trial, uint64_t *holes_out, uint64_t *board_out) {
     uint64_t used = dead_mask | board_mask;
@@ -399,23 +400,26 @@ int orc_deal_trial(const uint64_t *hole_masks, int n_seats, uint64_t board_mask,
     int live[52], n = 0;
     for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used) >> b) & 1ULL) live[n++] = b;
     const int nb = 5 - __builtin_popcountll(board_mask);
-    const int n_blocks = (2 * nr + 5 + 7) / 8;
+    const int n_steps = 2 * nr + 5, n_words = (n_steps + 2) / 3, n_blocks = (n_words + 3) / 4;
     const uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     for (uint32_t attempt = 0;; attempt++) {
-        uint32_t field[32];
+        uint32_t word[16];
         for (int b = 0; b < n_blocks; b++) {
-            const uint32_t ctr[4] = {(uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL3};
-            uint32_t w[4];
-            orc_philox4x32_10(ctr, key, w);
-            for (int j = 0; j < 4; j++) { field[8 * b + 2 * j] = w[j] & 0xFFFFu; field[8 * b + 2 * j + 1] = w[j] >> 16; }
+            const uint32_t ctr[4] = {(uint32_t)trial, (uint32_t)(trial >> 32), (uint32_t)b | (attempt << 8), TAG_DEAL4};
+            orc_philox4x32_10(ctr, key, word + 4 * b);
         }
         int deck[52], rejected = 0;
         for (int i = 0; i < n; i++) deck[i] = live[i];
-        for (int i = 0; i < 2 * nr + nb; i++) {               /* deck position == field index == step */
-            const uint32_t m = (uint32_t)(n - i), x = field[i] * m;
-            if ((x & 0xFFFFu) < 65536u % m) { rejected = 1; break; }
-            const int j = i + (int)(x >> 16);
-            const int c = deck[j]; deck[j] = deck[i]; deck[i] = c;
+        for (int w = 0; w < n_words && !rejected; w++) {
+            uint64_t r = word[w], M = 1;
+            for (int i = 3 * w; i < 3 * w + 3 && i < n_steps; i++) {
+                if (i >= 2 * nr + nb) continue;                 /* community card already known */
+                const uint64_t m = (uint64_t)(n - i), x = r * m;
+                const int j = i + (int)(x >> 32);
+                r = x & 0xFFFFFFFFULL; M *= m;
+                const int c = deck[j]; deck[j] = deck[i]; deck[i] = c;
+            }
+            if (r < (1ULL << 32) % M) rejected = 1;
         }
         if (rejected) continue;
         for (int i = 0; i < 2 * nr; i++) holes_out[rseat[i % nr]] |= 1ULL << deck[i];
