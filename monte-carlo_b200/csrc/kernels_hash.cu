@@ -436,9 +436,11 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
                     const CardKey *__restrict__ g_card, long long *__restrict__ d_counts) {
     using SH = McShape<NR>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned char *sdeck = smem_raw;                                                         // [13 words][512 threads]
-    uint2 *srep = reinterpret_cast<uint2 *>(smem_raw + 13 * MC_T4);                          // [64 cards][32 lanes]
-    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw + 13 * MC_T4 + 64 * 32 * sizeof(uint2));
+    __shared__ __align__(16) unsigned char sdeck[13 * MC_T4];                                // [13 words][512 threads]; static: its
+                                                                                             // address is an immediate of every LDS / STS
+    unsigned char *srep_b = smem_raw;                                                        // [64 cards][32 lanes] x 8 B
+    uint2 *srep = reinterpret_cast<uint2 *>(srep_b);
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw + 64 * 32 * sizeof(uint2));
     unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words + the mbarrier
     BulkStage stage;
     stage.start(sred + 19, H, g_blob, (uint32_t)sizeof(HashBlob));
@@ -452,7 +454,9 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 
     const uint32_t tid4 = 4u * threadIdx.x;
     unsigned char *dk = sdeck + tid4;
-    const uint2 *rep = srep + (threadIdx.x & 31);
+    const uint32_t lane8 = 8u * (threadIdx.x & 31);
+    // table entry of card a for this lane: byte address a * 256 + lane * 8, built by one PRMT
+    auto rep_of = [&](uint32_t a) -> uint2 { return *reinterpret_cast<const uint2 *>(srep_b + __byte_perm(a, lane8, 0x5504)); };
     const int nb = prm.n_board, nf = prm.n_fixed;
     uint32_t dinit[13];
 #pragma unroll
@@ -498,7 +502,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 #pragma unroll
         for (int k = 0; k < 5; k++) {
             eb[k] = make_uint2(0u, 0u);
-            if (k < nb) { eb[k] = rep[card[2 * NR + k] * 32]; b.t += eb[k].x; b.sn += eb[k].y; }      // (high half of the sum is never read)
+            if (k < nb) { eb[k] = rep_of(card[2 * NR + k]); b.t += eb[k].x; b.sn += eb[k].y; }      // (high half of the sum is never read)
         }
         // a seat can only flush in a suit the board holds >= 3 of: cbit = that suit's counter bit (0 if none)
         const uint32_t cbit = ((b.sn + 0x2222u) & 0x8888u) >> 3;
@@ -510,7 +514,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         uint32_t key[MAX_SEATS];
 #pragma unroll
         for (int q = 0; q < NR; q++) {
-            const uint2 e1 = rep[card[q] * 32], e2 = rep[card[q + NR] * 32];
+            const uint2 e1 = rep_of(card[q]), e2 = rep_of(card[q + NR]);
             const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + e1.y + e2.y;
             uint32_t k = H->V[ht_slot(t, H->D[ht_bucket(t)])];
             if (sn & 0x8888u) {
@@ -565,7 +569,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     }
 }
 
-static size_t mc_smem() { return 13 * MC_T4 + 64 * 32 * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
+static size_t mc_smem() { return 64 * 32 * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
 
 template <int NR>
 static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
