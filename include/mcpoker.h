@@ -82,6 +82,15 @@ int  mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
 int  mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
                         uint32_t *keys, int32_t *group_of, int32_t *n_groups);
 
+/* pot settlement of end-game: update-stacks gameplay.clj:104-116 over the Bet records of bet.clj:7-8.  Pure integer
+ * host arithmetic (no evaluation): for every pot, the FIRST tie group (group_of ascending = best first) that holds one
+ * of the pot's players wins it, and each of its members IN the pot receives int(bet * n / members) chips (:110-112,
+ * truncating division; the remainder is dropped exactly as the reference drops it).  pot_players = bitmask of seats.
+ * delta[seat] is accumulated into.  A pot none of whose players holds cards fails with MC_ERR_INVALID (the reference
+ * divides by zero there). */
+int  mc_settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
+                    const uint32_t *pot_players, int n_pots, int64_t *delta);
+
 /* ---- synthetic inputs (BASELINE config 1: Philox-seeded random hands, identical on CPU and GPU) --- */
 int  mc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *masks);
 int  mc_random_hands_dev(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks, void *stream);

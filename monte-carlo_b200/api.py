@@ -71,6 +71,20 @@ def showdown(board_mask, hole_masks):
     return list(keys[:n]), rc, list(groups[:n]), ng.value
 
 
+def settle_pots(group_of, pots):
+    """update-stacks (gameplay.clj:104-116): group_of[seat] = tie group (0 best, -1 = not at the showdown);
+    pots = [(bet, n, [seats])] -> chips won per seat"""
+    n = len(group_of)
+    g = (C.c_int32 * n)(*group_of)
+    k = len(pots)
+    bet = (C.c_int64 * max(k, 1))(*[p[0] for p in pots])
+    cnt = (C.c_int32 * max(k, 1))(*[p[1] for p in pots])
+    msk = (C.c_uint32 * max(k, 1))(*[sum(1 << s for s in p[2]) for p in pots])
+    delta = (C.c_int64 * n)()
+    E.check(E.lib().mc_settle_pots(g, n, bet, cnt, msk, k, delta))
+    return list(delta)
+
+
 def enumerate7(first=None, count=None, key_sum=True):
     E.ensure_init()
     hist, ks = (C.c_uint64 * 9)(), C.c_uint64(0)

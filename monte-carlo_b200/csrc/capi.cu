@@ -408,6 +408,23 @@ int mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, ui
     return MC_OK;
 }
 
+int mc_settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
+                   const uint32_t *pot_players, int n_pots, int64_t *delta) {
+    if (!group_of || !delta || n_seats < 1 || n_seats > MC_MAX_SEATS || n_pots < 0) return fail(MC_ERR_INVALID, "bad argument");
+    if (n_pots && (!pot_bet || !pot_n || !pot_players)) return fail(MC_ERR_INVALID, "null pot array");
+    for (int p = 0; p < n_pots; p++) {
+        int best_group = -1;                                     // lowest group index among the pot's players
+        for (int s = 0; s < n_seats; s++)
+            if ((pot_players[p] >> s) & 1u) { if (group_of[s] < 0) continue; if (best_group < 0 || group_of[s] < best_group) best_group = group_of[s]; }
+        if (best_group < 0) return fail(MC_ERR_INVALID, "a pot has no player at the showdown (the reference divides by zero here, gameplay.clj:112)");
+        int members = 0;
+        for (int s = 0; s < n_seats; s++) if (((pot_players[p] >> s) & 1u) && group_of[s] == best_group) members++;
+        const int64_t share = (pot_bet[p] * (int64_t)pot_n[p]) / members;          // int(/ total-pot (count pot-winners))
+        for (int s = 0; s < n_seats; s++) if (((pot_players[p] >> s) & 1u) && group_of[s] == best_group) delta[s] += share;
+    }
+    return MC_OK;
+}
+
 // ---- synthetic hands ------------------------------------------------------------------------------
 int mc_random_hands_dev(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks, void *stream) {
     if (n_cards < 1 || n_cards > 7) return fail(MC_ERR_INVALID, "n_cards must be 1..7");

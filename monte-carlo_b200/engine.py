@@ -19,7 +19,7 @@ EXPORTS = [
     "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version",
     "mc_card_bit", "mc_key_packed_to_nibble", "mc_key_decode",
     "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
-    "mc_showdown", "mc_showdown_groups", "mc_random_hands", "mc_random_hands_dev",
+    "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_random_hands", "mc_random_hands_dev",
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
     "mc_equity_mc", "mc_equity_mc_dev", "mc_preflop_matrix", "mc_preflop_matrix_part", "mc_preflop_cells",
@@ -71,6 +71,7 @@ def lib():
     L.mc_eval7_batch_dev_fmt.argtypes = [vp, sz, vp, C.c_int, vp]
     L.mc_showdown.argtypes = [u64, P(u64), C.c_int, P(u32), P(u32)]
     L.mc_showdown_groups.argtypes = [u64, P(u64), C.c_int, P(u32), P(i32), P(i32)]
+    L.mc_settle_pots.argtypes = [P(i32), C.c_int, P(i64), P(i32), P(u32), C.c_int, P(i64)]
     L.mc_random_hands.argtypes = [u64, u64, sz, C.c_int, vp]
     L.mc_random_hands_dev.argtypes = [u64, u64, sz, C.c_int, vp, vp]
     L.mc_enumerate7.argtypes = [P(u64), P(u64)]

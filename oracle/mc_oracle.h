@@ -73,6 +73,10 @@ int  orc_player_hand_value(const orc_card *cards, int n, orc_value *out, int *wo
  * group_of[seat] = index of its tie group (0 = best).  returns number of groups. */
 int  orc_group_winners(const uint32_t *keys, int n_seats, int *group_of);
 
+/* update-stacks :104-116: winner_sets[g] = seat bitmask of tie group g (best first); stack[seat] += share */
+int  orc_update_stacks(const unsigned *winner_sets, int n_groups, const long long *pot_bet, const int *pot_n,
+                       const unsigned *pot_players, int n_pots, long long *stack);
+
 uint32_t orc_value_to_key(const orc_value *v);
 void     orc_key_to_value(uint32_t key, orc_value *v);
 

@@ -231,6 +231,29 @@ int orc_group_winners(const uint32_t *keys, int n_seats, int *group_of) {
     return groups;
 }
 
+/* update-stacks, gameplay.clj:104-116, statement by statement.  winners = the tie groups as sets of seats, best first
+ * (group-winners); a pot = Bet{bet players n} (bet.clj:7-8), players as a seat set.
+ *   pot-intersections = (map intersection (repeat (:players pot)) winners)        :107-109
+ *   pot-winners       = (first (filter not-empty pot-intersections))               :110
+ *   pot-share         = (int (/ (* bet n) (count pot-winners)))                    :111-112
+ *   every p in pot-winners gets + pot-share                                        :113-116
+ * returns 0, or -1 where the reference would throw (no intersection -> (count nil) = 0 -> divide by zero). */
+int orc_update_stacks(const unsigned *winner_sets, int n_groups, const long long *pot_bet, const int *pot_n,
+                      const unsigned *pot_players, int n_pots, long long *stack /* by seat */) {
+    for (int p = 0; p < n_pots; p++) {
+        unsigned pot_winners = 0;
+        for (int g = 0; g < n_groups; g++) {
+            const unsigned inter = pot_players[p] & winner_sets[g];
+            if (inter) { pot_winners = inter; break; }
+        }
+        if (!pot_winners) return -1;
+        const long long total_pot = pot_bet[p] * (long long)pot_n[p];
+        const long long pot_share = total_pot / __builtin_popcount(pot_winners);     /* (int (/ a b)) truncates */
+        for (int seat = 0; seat < 32; seat++) if ((pot_winners >> seat) & 1u) stack[seat] += pot_share;
+    }
+    return 0;
+}
+
 /* key <-> value (hit lengths per category) */
 static const int HIT_LEN[9] = {5, 2, 4, 3, 5, 5, 5, 4, 5};
 uint32_t orc_value_to_key(const orc_value *v) {

@@ -48,6 +48,7 @@ def lib():
     L.orc_compare.argtypes = [P(Value), P(Value), P(i32)]
     L.orc_player_hand_value.argtypes = [P(Card), i32, P(Value), P(i32)]
     L.orc_group_winners.argtypes = [P(u32), i32, P(i32)]
+    L.orc_update_stacks.argtypes = [P(C.c_uint), i32, P(C.c_longlong), P(C.c_int), P(C.c_uint), i32, P(C.c_longlong)]
     L.orc_value_to_key.argtypes = [P(Value)]
     L.orc_value_to_key.restype = u32
     L.orc_key_to_value.argtypes = [u32, P(Value)]

@@ -319,3 +319,34 @@ def test_preflop_matrix_full_properties(gpu):
     p1, n1 = api.preflop_matrix_part(1, 3)
     p2, n2 = api.preflop_matrix_part(2, 3)
     assert np.array_equal(p0 + p1 + p2, m) and n0 + n1 + n2 > 40000
+
+
+def test_abi_is_thread_safe(gpu, oracle):
+    """the reference calls the evaluator from one go-block per room (board.clj:122-129): many host threads at once"""
+    import threading
+    api = gpu.api
+    masks = oracle.random_hands(SEED + 3, 0, 20000)
+    want = oracle.eval_batch(masks, 0)
+    holes = [api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50])]
+    errors = []
+
+    def worker(k):
+        try:
+            for it in range(20):
+                lo = (k * 997 + it * 131) % 15000
+                if not np.array_equal(api.eval7_batch(masks[lo:lo + 4000]), want[lo:lo + 4000]):
+                    errors.append("batch %d/%d" % (k, it))
+                w, t, l, nb = api.equity_exhaustive(holes)
+                if (w[0], w[1], t[0]) != (1388072, 318176, 6056):
+                    errors.append("equity %d/%d" % (k, it))
+                if api.key_decode(api.eval_cards([0, 0, 0, 0, 0], [9, 8, 7, 6, 5])) != [8, [9, 8, 7, 6, 5], []]:
+                    errors.append("single %d/%d" % (k, it))
+        except Exception as e:                      # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(6)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors[:5]

@@ -120,3 +120,35 @@ def test_product_evaluator_formulation_on_every_hand(oracle):
         out = subprocess.run([exe, arg], capture_output=True, text=True)
         assert out.returncode == 0, out.stdout + out.stderr
         assert "mismatches=0" in out.stdout
+
+
+def test_settle_pots_matches_oracle_and_mirror(pkg, oracle):
+    """mc_settle_pots (update-stacks, gameplay.clj:104-116) == the oracle's literal restatement == the Python mirror,
+    on random side-pot structures; pure host integer arithmetic, so it runs without a GPU."""
+    import random
+    rnd = random.Random(11)
+    for _ in range(300):
+        n = rnd.randint(2, 9)
+        n_groups = rnd.randint(1, n)
+        group_of = [rnd.randrange(n_groups) for _ in range(n)]
+        used = sorted(set(group_of))
+        group_of = [used.index(g) for g in group_of]                     # groups 0..k-1, all non-empty
+        pots = []
+        for _ in range(rnd.randint(0, 4)):
+            players = rnd.sample(range(n), rnd.randint(1, n))
+            pots.append((rnd.randint(1, 500), rnd.randint(1, n), players))
+        got = pkg.api.settle_pots(group_of, pots)
+        sets = [sum(1 << s for s in range(n) if group_of[s] == g) for g in range(len(used))]
+        stack = (C.c_longlong * 32)()
+        rc = oracle.lib().orc_update_stacks((C.c_uint * len(sets))(*sets), len(sets),
+                                            (C.c_longlong * max(1, len(pots)))(*[p[0] for p in pots]),
+                                            (C.c_int * max(1, len(pots)))(*[p[1] for p in pots]),
+                                            (C.c_uint * max(1, len(pots)))(*[sum(1 << s for s in p[2]) for p in pots]),
+                                            len(pots), stack)
+        assert rc == 0 and got == list(stack[:n])
+        winners = [{s for s in range(n) if group_of[s] == g} for g in range(len(used))]
+        mirror = pkg.gameplay.update_stacks([{"bet": b, "n": k, "players": set(pl)} for b, k, pl in pots], winners, {})
+        assert got == [mirror.get(s, 0) for s in range(n)]
+    # a pot whose players all folded: the reference divides by zero; the ABI reports MC_ERR_INVALID
+    with pytest.raises(pkg.engine.McError):
+        pkg.api.settle_pots([0, -1], [(10, 2, [1])])
