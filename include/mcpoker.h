@@ -123,6 +123,15 @@ int  mc_equity_mc_dev(const uint64_t *hole_masks /* host */, int n_seats, uint64
                       uint64_t seed, uint64_t first_trial, uint64_t n_trials,
                       int64_t *d_counts /* 27 int64, accumulated into */, void *stream);
 
+/* ---- heads-up range vs range on a (partial) board ------------------------------------- */
+/* A hole is indexed by the colex rank of its two card ids: idx = c0 + c1*(c1-1)/2, c0 < c1 (0..1325).  Every pair of
+ * disjoint holes (a from range A, b from range B, neither touching board | dead) with weight_a[a] * weight_b[b] != 0 is
+ * played out over every completion of the board; wtl = {win, tie, loss} of side A and *total, all weighted by the
+ * product of the two weights (weights 0..32767).  All devices of the library instance share the matchup list. */
+#define MC_N_HOLES 1326
+int  mc_equity_ranges(const int32_t *weight_a /* 1326 */, const int32_t *weight_b /* 1326 */, uint64_t board_mask,
+                      uint64_t dead_mask, int64_t wtl[3], int64_t *total /* nullable */);
+
 /* ---- 169 x 169 preflop matrix (K5) -------------------------------------------------------------- */
 /* class id: x = rank-2; pair 13x+x; suited (hi>lo) 13*hi+lo; offsuit 13*lo+hi.  wtl[a][b] = {win,tie,loss} of a */
 int  mc_preflop_matrix(int64_t *wtl /* 169*169*3 */);

@@ -123,6 +123,22 @@ def equity_mc(hole_masks, board_mask, dead_mask, seed, first_trial, n_trials):
     return list(w[:n]), list(t[:n]), list(l[:n])
 
 
+def hole_index(card_a, card_b):
+    """colex rank of a two-card hole over card ids (0..1325)"""
+    c0, c1 = min(card_a, card_b), max(card_a, card_b)
+    return c0 + c1 * (c1 - 1) // 2
+
+
+def equity_ranges(weight_a, weight_b, board_mask=0, dead_mask=0):
+    """heads-up range vs range: weights per hole index (1326 each) -> ([win, tie, loss] of A, total), weighted"""
+    E.ensure_init()
+    wa = (C.c_int32 * 1326)(*weight_a)
+    wb = (C.c_int32 * 1326)(*weight_b)
+    out, tot = (C.c_int64 * 3)(), C.c_int64(0)
+    E.check(E.lib().mc_equity_ranges(wa, wb, board_mask, dead_mask, out, C.byref(tot)))
+    return list(out), tot.value
+
+
 def preflop_cells(cells):
     E.ensure_init()
     n = len(cells)

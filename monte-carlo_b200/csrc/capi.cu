@@ -657,6 +657,62 @@ int run_matchups(const std::vector<Matchup> &mus, std::vector<long long> *wtl_fu
 }
 }  // namespace
 
+int mc_equity_ranges(const int32_t *weight_a, const int32_t *weight_b, uint64_t board_mask, uint64_t dead_mask,
+                     int64_t wtl[3], int64_t *total) {
+    int rc = need_init();
+    if (rc) return rc;
+    if (!weight_a || !weight_b || !wtl) return fail(MC_ERR_INVALID, "null argument");
+    if ((board_mask & ~DECK_MASK) || (dead_mask & ~DECK_MASK) || (board_mask & dead_mask)) return fail(MC_ERR_INVALID, "bad board / dead mask");
+    if (__builtin_popcountll(board_mask) > 5) return fail(MC_ERR_INVALID, "more than 5 community cards");
+    std::vector<std::pair<uint64_t, int32_t>> ra, rb;
+    for (int c1 = 1, idx = 0; c1 < 52; c1++)
+        for (int c0 = 0; c0 < c1; c0++, idx++) {
+            const uint64_t h = mc_card_bit(c0) | mc_card_bit(c1);
+            if (weight_a[idx] < 0 || weight_a[idx] > 32767 || weight_b[idx] < 0 || weight_b[idx] > 32767) return fail(MC_ERR_INVALID, "weights must be 0..32767");
+            if (h & (board_mask | dead_mask)) continue;
+            if (weight_a[idx]) ra.emplace_back(h, weight_a[idx]);
+            if (weight_b[idx]) rb.emplace_back(h, weight_b[idx]);
+        }
+    std::vector<Matchup> mus;
+    for (auto &a : ra) for (auto &b : rb) {
+        if (a.first & b.first) continue;
+        Matchup m; m.hole_a = a.first; m.hole_b = b.first; m.cell_ab = 0; m.cell_ba = 0; m.weight = (int64_t)a.second * b.second;
+        mus.push_back(m);
+    }
+    if (52 - __builtin_popcountll(board_mask | dead_mask) - 4 < 5 - __builtin_popcountll(board_mask)) return fail(MC_ERR_INVALID, "not enough live cards");
+    const int nd = (int)g_ctx.size();
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    const size_t per = (mus.size() + nd - 1) / nd;
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        const size_t lo = std::min(mus.size(), per * d), hi = std::min(mus.size(), lo + per);
+        CU(cudaSetDevice(c.device));
+        CU(cudaMemsetAsync(c.d_small, 0, SMALL_WORDS * sizeof(unsigned long long), c.stream));
+        if (hi > lo) {
+            if (c.matchup_cap < hi - lo) {
+                if (c.d_matchups) cudaFree(c.d_matchups);
+                c.d_matchups = nullptr; c.matchup_cap = 0;
+                CU(cudaMalloc(&c.d_matchups, (hi - lo) * sizeof(Matchup)));
+                c.matchup_cap = hi - lo;
+            }
+            CU(cudaMemcpyAsync(c.d_matchups, mus.data() + lo, (hi - lo) * sizeof(Matchup), cudaMemcpyHostToDevice, c.stream));
+            CU(launch_range_equity(c.d_matchups, (int)(hi - lo), board_mask, dead_mask, reinterpret_cast<long long *>(c.d_small), c.tb, c.info, c.stream));
+        }
+        CU(cudaMemcpyAsync(c.h_small, c.d_small, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    }
+    int64_t sum[4] = {0, 0, 0, 0};
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        CU(cudaSetDevice(c.device));
+        CU(cudaStreamSynchronize(c.stream));
+        for (int i = 0; i < 4; i++) sum[i] += (int64_t)c.h_small[i];
+    }
+    wtl[0] = sum[0]; wtl[1] = sum[1]; wtl[2] = sum[2];
+    if (total) *total = sum[3];
+    return MC_OK;
+}
+
 int mc_preflop_matrix(int64_t *wtl) {
     if (!wtl) return fail(MC_ERR_INVALID, "wtl is null");
     std::vector<Matchup> mus;

@@ -60,6 +60,10 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
 cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
                                 const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
 
+// d_out: win, tie, loss of side A and the total, weighted by Matchup::weight (4 x int64, accumulated into)
+cudaError_t launch_range_equity(const Matchup *d_matchups, int n_matchups, uint64_t board, uint64_t dead, long long *d_out,
+                                const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+
 uint64_t host_binom(int n, int k);
 
 }  // namespace mcp

@@ -291,6 +291,111 @@ cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long 
 }
 
 // ---------------------------------------------------------------------------------------------------
+// K6: heads-up range vs range on a (partial) board.  One WARP per weighted matchup: its lanes split the
+// C(n_live, K) board completions into equal contiguous index ranges; each warp keeps its own live-card list.
+// out = win, tie, loss of side A and the total, each weighted by the matchup weight (4 x int64, accumulated into).
+// ---------------------------------------------------------------------------------------------------
+constexpr int RNG_WARPS = HASH_THREADS / 32;
+
+template <int K>
+__global__ void __launch_bounds__(HASH_THREADS, 1)
+range_equity_kernel(const Matchup *__restrict__ mus, int n_mu, uint64_t board, uint64_t dead,
+                    const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card, long long *__restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *slive_all = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));             // [RNG_WARPS][LIVE_MAX]
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(slive_all + RNG_WARPS * LIVE_MAX);
+    __shared__ CardKey scard[64];
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
+    fill_binom(sbin);
+    if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
+    stage.wait();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint4 *slive = slive_all + warp * LIVE_MAX;
+    HandState base{0, SN_BIAS, (uint32_t)board, (uint32_t)(board >> 32)};
+    {
+        uint64_t x = board;
+        while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; base.t += scard[p].rk; base.sn += scard[p].sn; }
+    }
+    unsigned long long wa = 0, wb = 0, tie = 0, tot = 0;
+    const int gw = blockIdx.x * RNG_WARPS + warp, nw = gridDim.x * RNG_WARPS;
+    for (int mi = gw; mi < n_mu; mi += nw) {
+        const Matchup mu = mus[mi];
+        const uint64_t livem = DECK_MASK & ~(mu.hole_a | mu.hole_b | board | dead);
+        const int nl = __popcll(livem);
+        __syncwarp();
+        for (int p = lane; p < 64; p += 32) {
+            if ((livem >> p) & 1ull) slive[__popcll(livem & ((1ull << p) - 1ull))] = live_entry(scard[p], p);
+        }
+        if (lane < LIVE_MAX - nl && nl + lane < LIVE_MAX) slive[nl + lane] = make_uint4(0, 0, 0, 0);
+        HandState ha{0, 0, (uint32_t)mu.hole_a, (uint32_t)(mu.hole_a >> 32)}, hb{0, 0, (uint32_t)mu.hole_b, (uint32_t)(mu.hole_b >> 32)};
+        {
+            uint64_t x = mu.hole_a;
+            while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; ha.t += scard[p].rk; ha.sn += scard[p].sn; }
+            x = mu.hole_b;
+            while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; hb.t += scard[p].rk; hb.sn += scard[p].sn; }
+        }
+        __syncwarp();
+        const uint32_t total = K == 0 ? 1u : sbin[nl * BIN_K + K];
+        const uint32_t per = (total + 31u) / 32u;
+        const uint32_t lo = min(total, per * (uint32_t)lane), hi = min(total, lo + per);
+        uint32_t ca = 0, cb = 0, ct = 0;
+        if (lo < hi) {
+            Walker<K> w;
+            w.init(lo, nl, sbin, slive, base);
+            for (uint32_t i = lo; i < hi; i++) {
+                const HandState b = w.hand();
+                const uint32_t ka = ht_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, H->D, H->F, H->V);
+                const uint32_t kb = ht_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, H->D, H->F, H->V);
+                ca += ka > kb; cb += kb > ka; ct += ka == kb;
+                w.next(slive, nl);
+            }
+        }
+        const unsigned long long wgt = (unsigned long long)mu.weight;
+        wa += wgt * ca; wb += wgt * cb; tie += wgt * ct; tot += wgt * (hi - lo);
+    }
+    wa = warp_sum64(wa); wb = warp_sum64(wb); tie = warp_sum64(tie); tot = warp_sum64(tot);
+    if (lane == 0) {
+        unsigned long long *o = reinterpret_cast<unsigned long long *>(out);
+        if (wa) atomicAdd(&o[0], wa);
+        if (tie) atomicAdd(&o[1], tie);
+        if (wb) atomicAdd(&o[2], wb);
+        if (tot) atomicAdd(&o[3], tot);
+    }
+}
+
+static size_t range_smem() { return sizeof(HashBlob) + RNG_WARPS * LIVE_MAX * sizeof(uint4) + BIN_N * BIN_K * sizeof(uint32_t); }
+
+template <int K>
+static cudaError_t launch_range_k(const Matchup *d_mu, int n_mu, uint64_t board, uint64_t dead, long long *d_out,
+                                  const DeviceTables &tb, int grid, cudaStream_t st) {
+    auto kern = range_equity_kernel<K>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)range_smem());
+    if (e != cudaSuccess) return e;
+    kern<<<grid, HASH_THREADS, range_smem(), st>>>(d_mu, n_mu, board, dead, tb.d_blob, tb.d_card, d_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_range_equity(const Matchup *d_matchups, int n_matchups, uint64_t board, uint64_t dead, long long *d_out,
+                                const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (n_matchups <= 0) return cudaSuccess;
+    const int want = (n_matchups + RNG_WARPS - 1) / RNG_WARPS;
+    const int grid = want < di.sm_count ? want : di.sm_count;
+    switch (5 - __builtin_popcountll(board)) {
+        case 0: return launch_range_k<0>(d_matchups, n_matchups, board, dead, d_out, tb, grid, st);
+        case 1: return launch_range_k<1>(d_matchups, n_matchups, board, dead, d_out, tb, grid, st);
+        case 2: return launch_range_k<2>(d_matchups, n_matchups, board, dead, d_out, tb, grid, st);
+        case 3: return launch_range_k<3>(d_matchups, n_matchups, board, dead, d_out, tb, grid, st);
+        case 4: return launch_range_k<4>(d_matchups, n_matchups, board, dead, d_out, tb, grid, st);
+        case 5: return launch_range_k<5>(d_matchups, n_matchups, board, dead, d_out, tb, grid, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // K2: all C(52,7) hands in colex order of card ids.  out = hist[9], sum of nibble keys (10 x u64).
 // ---------------------------------------------------------------------------------------------------
 constexpr int ENUM_FOLD = 32;         // hands between folds of the packed category counters (6-bit fields hold <= 32... 63)

@@ -350,3 +350,41 @@ def test_abi_is_thread_safe(gpu, oracle):
     for th in threads:
         th.join()
     assert not errors, errors[:5]
+
+
+def test_equity_ranges_vs_oracle(gpu, oracle):
+    """range vs range on flop / turn / river / preflop boards == sum of the oracle's exhaustive
+    equities over the weighted disjoint hole pairs"""
+    import random
+    api = gpu.api
+    rnd = random.Random(3)
+    for n_board, n_a, n_b in ((3, 25, 30), (4, 40, 40), (5, 60, 50), (0, 3, 3), (3, 1326, 8)):
+        cards = rnd.sample(range(52), n_board + 2)
+        board, dead = api.mask_of_ids(cards[:n_board]), api.mask_of_ids(cards[n_board:])
+        holes = [(a, b) for b in range(52) for a in range(b)]
+        wa, wb = [0] * 1326, [0] * 1326
+        for a, b in rnd.sample(holes, n_a):
+            wa[api.hole_index(a, b)] = rnd.randint(1, 9)
+        for a, b in rnd.sample(holes, n_b):
+            wb[api.hole_index(a, b)] = rnd.randint(1, 9)
+        got, total = api.equity_ranges(wa, wb, board, dead)
+        want, wtot = [0, 0, 0], 0
+        la = [(wa[api.hole_index(a, b)], api.mask_of_ids([a, b])) for a, b in holes if wa[api.hole_index(a, b)]]
+        lb = [(wb[api.hole_index(a, b)], api.mask_of_ids([a, b])) for a, b in holes if wb[api.hole_index(a, b)]]
+        for fa, ha in la:
+            if ha & (board | dead):
+                continue
+            for fb, hb in lb:
+                if hb & (board | dead | ha):
+                    continue
+                rc, w, t, l, nb = oracle.equity_exhaustive([ha, hb], board, dead)
+                want[0] += fa * fb * w[0]; want[1] += fa * fb * t[0]; want[2] += fa * fb * l[0]; wtot += fa * fb * nb
+        assert got == want and total == wtot and sum(got) == total
+    # AA vs KK as two one-class ranges, preflop = the golden class cell
+    wa, wb = [0] * 1326, [0] * 1326
+    for s in range(4):
+        for t in range(s):
+            wa[api.hole_index(13 * s + 12, 13 * t + 12)] = 1
+            wb[api.hole_index(13 * s + 11, 13 * t + 11)] = 1
+    got, total = api.equity_ranges(wa, wb)
+    assert got == [50371344, 267444, 11004156] and total == 36 * 1712304
