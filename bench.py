@@ -330,6 +330,19 @@ def run_ours(args):
         "roofline": {"bound": "int_issue", "ops_per_unit": OPS["mc9"], "achieved": rate4 * OPS["mc9"] / 1e12,
                      "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate4 * OPS["mc9"] / (world * int_peak)}}
 
+    # the reference's own call site: one showdown of a full table through the host ABI (latency-bound by design)
+    if rank == 0:
+        board9 = api.mask_of_ids([0, 15, 28, 48, 5])
+        holes_sd = (C.c_uint64 * 9)(*[api.mask_of_ids([6 + i, 29 + 2 * i]) for i in range(9)])
+        keys_sd, grp_sd, ng_sd = (C.c_uint32 * 9)(), (C.c_int32 * 9)(), C.c_int32(0)
+        for _ in range(20):
+            E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd)))
+        t0 = time.perf_counter()
+        for _ in range(500):
+            E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd)))
+        work["showdown_9_seats_host_call"] = {"latency_us": 1e6 * (time.perf_counter() - t0) / 500,
+                                              "note": "end-game ranking + group-winners of one table (gameplay.clj:127-132) per call; launch + 2 copies"}
+
     # config 5: the 169 x 169 preflop matrix, suit-canonical matchups dealt round-robin over the ranks, one all-reduce
     if not args.no_matrix:
         api.preflop_matrix_part(rank, world)                      # warm-up: builds and caches the matchup list

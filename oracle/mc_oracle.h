@@ -17,7 +17,7 @@
  *     org.clojure/clojure 1.4.0             compare on persistent vectors (APersistentVector.compareTo:
  *                                           length first, then element-wise Util.compare)
  * It is PINNED for the 5-card evaluator and its predicates by every assert of the reference's
- * test/montecarlo/hand_evaluator_test.clj (tests/test_oracle_reference_vectors.py).  The reference has
+ * test/montecarlo/hand_evaluator_test.clj (tests/golden/reference_vectors.json, tests/test_oracle.py).  The reference has
  * no test for 7-card ranking, showdown, or equity: those are "parity unpinned" by the reference and are
  * pinned here by composition (5-card value -> max under compare -> tie by =), with three independent
  * formulations (literal, rank-count best-of-21, direct bitmask) cross-checked exhaustively.
