@@ -92,6 +92,7 @@ void     orc_eval_batch(const uint64_t *masks, size_t n, uint32_t *keys, int whi
  * first/count select a sub-range of combination indices (count = 0 -> to the end). */
 int  orc_enumerate(int k, int which, int threads, uint64_t first, uint64_t count,
                    uint64_t hist[9], uint64_t *key_sum, uint64_t *n_distinct);
+int  orc_enumerate_masks(int k, uint64_t first, uint64_t count, int threads, uint64_t *masks);
 /* same enumeration but compares the two fast formulations hand by hand; returns #mismatches */
 uint64_t orc_enumerate_crosscheck(int k, int threads);
 

@@ -248,6 +248,28 @@ int orc_enumerate(int k, int which, int threads, uint64_t first, uint64_t count,
     return 0;
 }
 
+/* the masks of combinations first .. first+count-1 (same colex order as orc_enumerate), for key-by-key checks */
+int orc_enumerate_masks(int k, uint64_t first, uint64_t count, int threads, uint64_t *masks) {
+    if (k < 1 || k > 7) return -1;
+    binom_init(); cards_init();
+    if (first > BINOM[52][k] || count > BINOM[52][k] - first) return -1;
+    int nt = use_threads(threads);
+    uint64_t chunk = (count + (uint64_t)nt - 1) / (uint64_t)nt;
+#pragma omp parallel for num_threads(nt) schedule(static, 1)
+    for (int t = 0; t < nt; t++) {
+        uint64_t lo = chunk * (uint64_t)t, hi = lo + chunk > count ? count : lo + chunk;
+        if (lo >= hi) continue;
+        int c[7]; colex_unrank(first + lo, k, c);
+        for (uint64_t i = lo; i < hi; i++) {
+            uint64_t m = 0;
+            for (int j = 0; j < k; j++) m |= CARD_BIT[c[j]];
+            masks[i] = m;
+            colex_next(c, k, 52);
+        }
+    }
+    return 0;
+}
+
 uint64_t orc_enumerate_crosscheck(int k, int threads) {
     if (k < 5 || k > 7) return ~0ULL;
     binom_init(); cards_init();

@@ -134,6 +134,15 @@ def enumerate_hands(k, which=0, threads=0, first=0, count=0, distinct=False):
     return list(hist), ks.value, (nd.value if distinct else None)
 
 
+def enumerate_masks(k, first, count, threads=0):
+    import numpy as np
+    out = np.empty(count, dtype=np.uint64)
+    L = lib()
+    L.orc_enumerate_masks.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p]
+    assert L.orc_enumerate_masks(k, first, count, threads, out.ctypes.data) == 0
+    return out
+
+
 def equity_exhaustive(holes, board=0, dead=0, threads=0):
     n = len(holes)
     h = (C.c_uint64 * n)(*holes)

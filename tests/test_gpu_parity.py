@@ -137,6 +137,17 @@ def test_k1_on_structured_hand_families(gpu, oracle):
         assert np.array_equal(gpu.api.eval7_batch(masks, key_format=4), oracle.eval_batch(masks, 0))
 
 
+def test_k1_every_seven_card_hand_key_by_key(gpu, oracle):
+    """BASELINE target: 100 % bit-exact rank agreement on all 133,784,560 seven-card hands, key by key, through the
+    host-buffer ABI call (K1 v3 for these batch sizes) against the oracle's direct evaluator"""
+    total, step, bad = 133784560, 1 << 24, 0
+    for first in range(0, total, step):
+        n = min(step, total - first)
+        masks = oracle.enumerate_masks(7, first, n)
+        bad += int(np.count_nonzero(gpu.api.eval7_batch(masks) != oracle.eval_batch(masks, 0)))
+    assert bad == 0
+
+
 # ---- K2: exhaustive enumeration (BASELINE config 2) ---------------------------------------------------
 def test_enumerate7_goldens(gpu):
     hist, key_sum = gpu.api.enumerate7()
