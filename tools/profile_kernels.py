@@ -37,5 +37,8 @@ holes9 = (C.c_uint64 * 9)(api.mask_of_ids([12, 25]), 0, 0, 0, 0, 0, 0, 0, 0)
 for rep in range(2):
     E.check(L.mc_equity_exhaustive_dev(holes2, 2, 0, 0, 0, 1712304, cnt.data_ptr(), st))
     E.check(L.mc_equity_mc_dev(holes9, 9, 0, 0, 0x5EED5EED, 0, 1 << 26, cnt.data_ptr(), st))
+aa, kk = api.hole_class(14, 14, False), api.hole_class(13, 13, False)
+for rep in range(2):
+    cell = api.preflop_cells([(aa, kk)])          # 3 suit-canonical matchups x 1,712,304 boards
 torch.cuda.synchronize()
-print("ok", out[:9].tolist())
+print("ok", out[:9].tolist(), cell.tolist())
