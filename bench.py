@@ -405,7 +405,7 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "eval7_stream_hash_kernel", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
-                         "int_issue_frac_at_64_ops": (value / world) * OPS["eval"] / int_peak},
+                         "int_issue_frac": (value / world) * OPS["eval"] / int_peak, "ops_per_eval": OPS["eval"]},
             "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
                     "hands_per_step": ne, "call": "mc_eval7_batch (pinned host buffers, 3-stage copy/compute pipeline)"},
             "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
