@@ -242,7 +242,7 @@ def run_ours(args):
             raise SystemExit("K1 keys differ from the oracle: refusing to report a number")
     variants = {}
     for name, fmt in (("packed_key_bitplane", E.KEY_PACKED), ("nibble_flo_bitplane", E.KEY_NIBBLE_FLO),
-                      ("nibble_rankset_table_v2", E.KEY_NIBBLE_TABLE), ("nibble_hash_v3", E.KEY_NIBBLE_HASH)):
+                      ("nibble_rankset_table_v2", E.KEY_NIBBLE_TABLE), ("nibble_hash_v4", E.KEY_NIBBLE_HASH)):
         v_ms = timed_region(torch, dist, world, lambda: k1_step(fmt), max(2, args.steps // 2), 1)
         variants[name] = world * n * max(2, args.steps // 2) / (v_ms * 1e-3)
 

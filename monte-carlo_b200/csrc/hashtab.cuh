@@ -59,7 +59,8 @@ MCP_HD uint32_t ht_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi,
 }
 
 // ---- K1 layout ("stream blob"): everything the streaming kernel needs, in one shared-memory image ------------
-// [0, 64 KB)   256 rows of 256 B, row r = byte value r of the card mask:
+// [0, 64 KB)   256 rows of 256 B, row r = byte value r of a 16-bit rank set (a suit lane of the card mask, or a
+//              rank-count bit plane taken over the four lanes, which is how eval7_stream_hash_kernel reads it):
 //                  first half   TL[r] replicated for the 32 lanes (bank == lane: conflict-free for any mix of r);
 //                               TL[r] = sum of RKM[rank] over the bits of r read as ranks 0..7 (only r % 4 == 0 occur)
 //                  second half  TH[r] likewise for ranks 8..15 (only r < 128 occur)
@@ -67,7 +68,8 @@ MCP_HD uint32_t ht_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi,
 //              each) and the flush table (second halves of rows r >= 128, 64 u16 each)
 // [64 KB, +16 KB)  D as in HashBlob
 // [80 KB, ...)     V', same slots as HashBlob::V but holding the BYTE ADDRESS (< 65536) of the hand's nibble key
-// so a valid 7-card hand costs 8 conflict-free loads (t), D, V' and the key itself.
+// t is linear in the cards, so with count = c0 + 2*c1 + 4*c2 per rank, t = T(c0) + 2*T(c1) + 4*T(c2): a 7-card hand
+// without quads costs 4 conflict-free loads (t), D, V' and the key itself.
 constexpr uint32_t SB_ROWS_BYTES = 65536;
 constexpr uint32_t SB_D_OFF = SB_ROWS_BYTES;
 constexpr uint32_t SB_V_OFF = SB_D_OFF + HT_BUCKETS * 2;

@@ -106,21 +106,32 @@ static cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K1 v3: streaming evaluation through the additive-key / perfect-hash tables (hashtab.cuh "K1 layout").
-// A valid 7-card hand of the 52-card deck costs eight conflict-free byte-table loads (one PRMT each builds the
-// address: row = a byte of the mask, column = the lane), the displacement, the slot and the key; the ALU only
-// sums, finds a flush lane and checks validity.  Anything else (5/6 cards, the tests' rank 1, invalid masks)
-// takes the bit-plane evaluator of eval.cuh on a divergent slow path.
+// K1 v4: streaming evaluation through the additive-key / perfect-hash tables (hashtab.cuh "K1 layout").
+// A valid 7-card hand of the 52-card deck costs four conflict-free byte-table loads (one PRMT each builds the
+// address: row = a byte of a rank-count bit plane, column = the lane), the displacement, the slot and the key; the
+// ALU only adds the suit lanes into count planes, sums, finds a flush lane and checks validity.  Anything else
+// (quads, 5/6 cards, the tests' rank 1, invalid masks) is redone by k1h_general behind one divergent branch per
+// loop iteration; inputs are software-pipelined one iteration ahead.
 // ---------------------------------------------------------------------------------------------------
 constexpr int K1H_THREADS = 1024;
 
-__device__ __forceinline__ uint32_t k1h_key(uint64_t m, const unsigned char *sb, uint32_t lane4) {
+// shared-space loads by 32-bit address: the tables never change after staging, so these are plain (movable) asm
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+
+// The common case: a 7-card hand of the 52-card deck in which no rank appears four times.  `odd` is non-zero
+// for everything else (quads plane, bits outside the deck, card count != 7); such a hand is redone by
+// k1h_general.  sb32 = shared address of the stream blob, lane4 = 4 * lane.
+__device__ __forceinline__ uint32_t k1h_fast(uint64_t m, uint32_t sb32, uint32_t lane4, uint32_t &odd) {
     const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
-    auto row = [&](uint32_t w, uint32_t sel, uint32_t half) -> uint32_t {
-        return *reinterpret_cast<const uint32_t *>(sb + __byte_perm(w, lane4, sel) + half);
-    };
-    const uint32_t t = (row(lo, 0x5504, 0) + row(lo, 0x5514, 128) + row(lo, 0x5524, 0) + row(lo, 0x5534, 128)) +
-                       (row(hi, 0x5504, 0) + row(hi, 0x5514, 128) + row(hi, 0x5524, 0) + row(hi, 0x5534, 128));
+    // per-rank card counts over the four suit lanes as bit planes (carry-save): count = c0 + 2*c1 + 4*c2, so
+    // t = sum of count * RKM[rank] takes four byte-table loads (two bytes of c0, two of c1) instead of eight
+    const uint32_t x = lo ^ hi, y = lo & hi;                   // per lane pair: sum bit, carry bit
+    const uint32_t xs = __umulhi(x, 65536u), ys = __umulhi(y, 65536u);   // x >> 16 on the (idle) FMA pipe: the ALU pipe is the busy one
+    const uint32_t c0 = x ^ xs;                                // only the low 16 bits of the planes are read
+    const uint32_t c1 = (x & xs) ^ y ^ ys;
+    const uint32_t t = (lds_u32(sb32 + __byte_perm(c0, lane4, 0x5504)) + lds_u32(sb32 + 128u + __byte_perm(c0, lane4, 0x5514))) +
+                       2u * (lds_u32(sb32 + __byte_perm(c1, lane4, 0x5504)) + lds_u32(sb32 + 128u + __byte_perm(c1, lane4, 0x5514)));
     // flush lane: only the word holding >= 5 cards can contain it
     const int p01 = __popc(lo), p23 = __popc(hi);
     const bool up = p23 >= 5;
@@ -129,47 +140,82 @@ __device__ __forceinline__ uint32_t k1h_key(uint64_t m, const unsigned char *sb,
     const uint32_t wl = w & 0xFFFFu, wh = w >> 16;
     const int pl = __popc(wl), ph = pw - pl;
     const uint32_t fm = pl >= 5 ? wl : (ph >= 5 ? wh : 0u);
-    const uint32_t d = *reinterpret_cast<const uint16_t *>(sb + SB_D_OFF + (t & 0x3FFEu));
-    uint32_t ka = *reinterpret_cast<const uint16_t *>(sb + SB_V_OFF + 2u * ((t >> 16) + d));
-    if (fm) ka = *reinterpret_cast<const uint16_t *>(sb + sb_flush_addr((fm >> 2) & 0x1FFFu));   // masked: an invalid mask must stay inside the table
-    uint32_t key = *reinterpret_cast<const uint32_t *>(sb + ka);
-    const bool deck7 = (p01 + p23 == 7) && (((lo | hi) & 0x80038003u) == 0u);
-    if (!deck7) {
-        const uint32_t n = (uint32_t)(p01 + p23);
-        const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
-        key = ok ? packed_to_nibble(eval_packed(lo, hi)) : 0xFFFFFFFFu;
-    }
-    return key;
+    odd = (y & ys) | ((lo | hi) & 0x80038003u) | (uint32_t)(p01 + p23 - 7);      // ys has no high half, so y & ys is the quads plane
+    const uint32_t d = lds_u16(sb32 + SB_D_OFF + (t & 0x3FFEu));
+    uint32_t ka = lds_u16(sb32 + SB_V_OFF + 2u * ((t >> 16) + d));
+    // masked: whatever the mask holds, the address stays inside the table
+    if (fm) ka = lds_u16(sb32 + 0x8080u + (fm & 0x7F00u) + ((fm >> 1) & 0x7Eu));      // == sb_flush_addr(fm >> 2)
+    return lds_u32(sb32 + ka);
 }
 
+// any mask: quads, 5/6 cards, the tests' rank 1, invalid masks; also correct for the common case
+__device__ __noinline__ uint32_t k1h_general(uint64_t m, uint32_t sb32, uint32_t lane4) {
+    const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
+    const uint32_t n = (uint32_t)(__popc(lo) + __popc(hi));
+    if (n != 7u || ((lo | hi) & 0x80038003u)) {
+        const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
+        return ok ? packed_to_nibble(eval_packed(lo, hi)) : 0xFFFFFFFFu;
+    }
+    uint32_t t = 0, fm = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t w = k < 2 ? lo : hi, lane = (k & 1) ? (w >> 16) : (w & 0xFFFFu);
+        t += lds_u32(sb32 + ((lane & 0xFFu) << 8) + lane4) + lds_u32(sb32 + 128u + (lane & 0xFF00u) + lane4);
+        if (__popc(lane) >= 5) fm = lane;
+    }
+    const uint32_t d = lds_u16(sb32 + SB_D_OFF + (t & 0x3FFEu));
+    uint32_t ka = lds_u16(sb32 + SB_V_OFF + 2u * ((t >> 16) + d));
+    if (fm) ka = lds_u16(sb32 + sb_flush_addr(fm >> 2));
+    return lds_u32(sb32 + ka);
+}
+
+// one launch covers at most 2^31 hands, so every index fits 32 bits (the launcher cuts longer batches)
 __global__ void __launch_bounds__(K1H_THREADS, 1)
-eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, size_t n,
+eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, uint32_t n,
                          const uint4 *__restrict__ g_blob) {
     extern __shared__ __align__(16) unsigned char sb[];
     __shared__ unsigned long long mbar;
     BulkStage stage;
     stage.start(&mbar, sb, g_blob, SB_BYTES);
     stage.wait();
+    uint32_t sb32 = (uint32_t)__cvta_generic_to_shared(sb);
+    asm volatile("" : "+r"(sb32) : : "memory");               // every table load depends on this: none moves above the wait
     const uint32_t lane4 = (threadIdx.x & 31u) * 4u;
-    const size_t npair = n >> 1;
+    const uint32_t npair = n >> 1;
     const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);
     uint2 *out = reinterpret_cast<uint2 *>(keys);
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npair; i += 2 * stride) {
-        const size_t j = i + stride;
-        const bool two = j < npair;
-        const ulonglong2 a = __ldcs(in + i);
-        ulonglong2 b = make_ulonglong2(0ull, 0ull);
-        if (two) b = __ldcs(in + j);
-        uint2 ka, kb;
-        ka.x = k1h_key(a.x, sb, lane4);
-        ka.y = k1h_key(a.y, sb, lane4);
-        kb.x = k1h_key(b.x, sb, lane4);
-        kb.y = k1h_key(b.y, sb, lane4);
-        __stcs(out + i, ka);
-        if (two) __stcs(out + j, kb);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    // software pipeline: the next iteration's 32 bytes are requested before this iteration's four hands are
+    // evaluated, so every thread keeps loads in flight while it works (32 warps x 32 B per SM, issued only
+    // between evaluations, is less than bandwidth x latency).  Prefetch indices are clamped, not predicated.
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < npair) {
+        const uint32_t last = npair - 1u;
+        ulonglong2 a = __ldcs(in + i);
+        ulonglong2 b = __ldcs(in + min(i + stride, last));
+        for (; i < npair; i += 2 * stride) {
+            const uint32_t j = i + stride;
+            const ulonglong2 na = __ldcs(in + min(j + stride, last));
+            const ulonglong2 nb = __ldcs(in + min(j + 2 * stride, last));
+            uint32_t o0, o1, o2, o3;
+            uint2 ka, kb;
+            ka.x = k1h_fast(a.x, sb32, lane4, o0);
+            ka.y = k1h_fast(a.y, sb32, lane4, o1);
+            kb.x = k1h_fast(b.x, sb32, lane4, o2);
+            kb.y = k1h_fast(b.y, sb32, lane4, o3);
+            if (o0 | o1 | o2 | o3) {                          // one lane in ~150 per iteration: a single divergent branch
+                if (o0) ka.x = k1h_general(a.x, sb32, lane4);
+                if (o1) ka.y = k1h_general(a.y, sb32, lane4);
+                if (o2) kb.x = k1h_general(b.x, sb32, lane4);
+                if (o3) kb.y = k1h_general(b.y, sb32, lane4);
+            }
+            __stcs(out + i, ka);
+            if (j < npair) __stcs(out + j, kb);
+            a = na;
+            b = nb;
+        }
     }
-    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) keys[n - 1] = k1h_key(masks[n - 1], sb, lane4);
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) keys[n - 1] = k1h_general(masks[n - 1], sb32, lane4);
 }
 
 cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
@@ -177,10 +223,17 @@ cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t
     if (n == 0) return cudaSuccess;
     cudaError_t e = cudaFuncSetAttribute(eval7_stream_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_BYTES);
     if (e != cudaSuccess) return e;
-    size_t want = (n + (size_t)K1H_THREADS * 4 - 1) / ((size_t)K1H_THREADS * 4);
-    const int grid = (int)(want > (size_t)di.sm_count ? (size_t)di.sm_count : want);
-    eval7_stream_hash_kernel<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks, d_keys, n, reinterpret_cast<const uint4 *>(d_stream_blob));
-    return cudaGetLastError();
+    constexpr size_t CHUNK = (size_t)1 << 30;                 // hands per launch: even, so every chunk keeps the alignment
+    for (size_t off = 0; off < n; off += CHUNK) {
+        const size_t m = n - off < CHUNK ? n - off : CHUNK;
+        size_t want = (m + (size_t)K1H_THREADS * 4 - 1) / ((size_t)K1H_THREADS * 4);
+        const int grid = (int)(want > (size_t)di.sm_count ? (size_t)di.sm_count : want);
+        eval7_stream_hash_kernel<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks + off, d_keys + off, (uint32_t)m,
+                                                                      reinterpret_cast<const uint4 *>(d_stream_blob));
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 }
 
 cudaError_t launch_eval7_stream(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int mode,

@@ -46,7 +46,7 @@ struct DeviceTables {
     const HashBlob *d_blob = nullptr;        // device: D / F / V
     const CardKey *d_card = nullptr;         // device: 64 entries by bit position
     const uint32_t *d_nib = nullptr;         // device: dense class index -> nibble key
-    const void *d_stream_blob = nullptr;     // device: shared-memory image of the streaming kernel (K1 v3)
+    const void *d_stream_blob = nullptr;     // device: shared-memory image of the streaming kernel (K1)
     const CardKey *h_card = nullptr;         // host copy of d_card
     CatBase cat_base{};
     uint32_t n_classes = 0;

@@ -101,7 +101,7 @@ def test_eval7_batch_edge_cases(gpu, oracle):
 
 
 def test_eval7_batch_hash_kernel_slow_path_and_ragged(gpu, oracle):
-    """K1 v3 (key_format 4): 5/6-card hands, the tests' rank 1 and invalid masks leave the table path; odd sizes"""
+    """K1 hash kernel (key_format 4): 5/6-card hands, the tests' rank 1 and invalid masks leave the table path; odd sizes"""
     api = gpu.api
     base = oracle.random_hands(SEED + 7, 0, 50_001)
     mixed = np.concatenate([base, oracle.random_hands(SEED, 0, 3000, 5), oracle.random_hands(SEED, 0, 3000, 6),
@@ -139,7 +139,7 @@ def test_k1_on_structured_hand_families(gpu, oracle):
 
 def test_k1_every_seven_card_hand_key_by_key(gpu, oracle):
     """BASELINE target: 100 % bit-exact rank agreement on all 133,784,560 seven-card hands, key by key, through the
-    host-buffer ABI call (K1 v3 for these batch sizes) against the oracle's direct evaluator"""
+    host-buffer ABI call (the K1 hash kernel for these batch sizes) against the oracle's direct evaluator"""
     total, step, bad = 133784560, 1 << 24, 0
     for first in range(0, total, step):
         n = min(step, total - first)
