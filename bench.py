@@ -344,7 +344,16 @@ def run_ours(args):
         for _ in range(500):
             E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd)))
         work["showdown_9_seats_host_call"] = {"latency_us": 1e6 * (time.perf_counter() - t0) / 500,
-                                              "note": "end-game ranking + group-winners of one table (gameplay.clj:127-132) per call; launch + 2 copies"}
+                                              "note": "end-game ranking + group-winners of one table (gameplay.clj:127-132) per call; "
+                                                      "seats by kernel parameter, result written to mapped pinned host memory: one launch + one sync"}
+        suits1, ranks1, key1 = (C.c_int32 * 7)(0, 1, 2, 3, 0, 1, 2), (C.c_int32 * 7)(14, 14, 9, 8, 5, 3, 2), C.c_uint32(0)
+        for _ in range(20):
+            E.check(L.mc_eval_cards(suits1, ranks1, 7, C.byref(key1)))
+        t0 = time.perf_counter()
+        for _ in range(500):
+            E.check(L.mc_eval_cards(suits1, ranks1, 7, C.byref(key1)))
+        work["evaluator_one_hand_host_call"] = {"latency_us": 1e6 * (time.perf_counter() - t0) / 500, "key": "%06x" % key1.value,
+                                                "note": "player->hand-value of one 7-card hand (hand_evaluator.clj:162-172) per call"}
 
     # config 5: the 169 x 169 preflop matrix, suit-canonical matchups dealt round-robin over the ranks, one all-reduce
     if not args.no_matrix:

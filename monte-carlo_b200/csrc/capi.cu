@@ -9,6 +9,7 @@
 #include "hashtab_build.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -31,6 +32,7 @@ int cuda_fail(cudaError_t e, const char *what) {
 constexpr int N_SLOTS = 3;
 constexpr size_t SLOT_HANDS = 1u << 22;           // 4 Mi hands per pipeline stage: 32 MiB in, 16 MiB out
 constexpr int SMALL_WORDS = 64;
+static_assert(SMALL_TICKET_WORD < 2 * SMALL_WORDS && SMALL_TICKET_WORD >= 2 * 32, "ticket word inside the scratch, above every counts copy");
 
 struct DevCtx {
     int device = -1;
@@ -41,7 +43,9 @@ struct DevCtx {
     uint64_t *d_in[N_SLOTS] = {};
     uint32_t *d_out[N_SLOTS] = {};
     unsigned long long *d_small = nullptr;        // SMALL_WORDS x u64 scratch
-    unsigned long long *h_small = nullptr;        // pinned mirror
+    unsigned long long *h_small = nullptr;        // pinned mirror (mapped)
+    unsigned long long *hd_small = nullptr;       // the device's address of h_small
+    uint32_t ticket = 0;                          // sequence number of the single-call kernels (await_ticket)
     Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
     long long *d_wtl = nullptr;
     DeviceTables tb;                              // perfect-hash evaluator tables (hashtab.cuh), built at init
@@ -150,7 +154,8 @@ int init_devices(const int *ids, int n) {
         c->device = d;
         CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
         CU(cudaMalloc(&c->d_small, SMALL_WORDS * sizeof(unsigned long long)));
-        CU(cudaHostAlloc(&c->h_small, SMALL_WORDS * sizeof(unsigned long long), cudaHostAllocDefault));
+        CU(cudaHostAlloc(&c->h_small, SMALL_WORDS * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
+        CU(cudaHostGetDevicePointer(reinterpret_cast<void **>(&c->hd_small), c->h_small, 0));
         if (!g_tables) { rc = build_tables(*c); if (rc) return rc; }
         rc = upload_tables(*c);
         if (rc) return rc;
@@ -161,6 +166,20 @@ int init_devices(const int *ids, int n) {
 
 int need_init() {
     if (g_ctx.empty()) return fail(MC_ERR_NOT_INIT, "mc_init has not been called");
+    return MC_OK;
+}
+
+// Wait for a single-call kernel (launch_showdown / launch_eval_one writing into the mapped h_small): poll the ticket
+// word it writes last instead of paying the stream synchronisation; a kernel that never delivers (launch failure,
+// sticky error) is caught by the bounded spin falling back to cudaStreamSynchronize, which reports the error.
+int await_ticket(DevCtx &c, uint32_t ticket) {
+    volatile uint32_t *flag = reinterpret_cast<volatile uint32_t *>(c.h_small) + SMALL_TICKET_WORD;
+    for (int spin = 0; spin < 200000; spin++) {
+        if (*flag == ticket) { std::atomic_thread_fence(std::memory_order_acquire); return MC_OK; }
+        __builtin_ia32_pause();
+    }
+    CU(cudaStreamSynchronize(c.stream));
+    if (*flag != ticket) return fail(MC_ERR_CUDA, "single-call kernel finished without delivering its result");
     return MC_OK;
 }
 
@@ -372,12 +391,13 @@ int mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards, uint
     DevCtx &c = *g_ctx[0];
     std::lock_guard<std::mutex> lk(c.mu);
     CU(cudaSetDevice(c.device));
-    c.h_small[0] = m;
-    CU(cudaMemcpyAsync(c.d_small, c.h_small, 8, cudaMemcpyHostToDevice, c.stream));
-    CU(launch_eval7_stream(reinterpret_cast<const uint64_t *>(c.d_small), 1, reinterpret_cast<uint32_t *>(c.d_small + 2), K1_NIBBLE_FLO, c.info, c.stream));
-    CU(cudaMemcpyAsync(c.h_small + 2, c.d_small + 2, 8, cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaStreamSynchronize(c.stream));
-    *key = (uint32_t)c.h_small[2];
+    // the mask travels as a kernel parameter and the key is written straight into mapped pinned host memory:
+    // one launch and one stream sync, no copies
+    const uint32_t ticket = ++c.ticket;
+    CU(launch_eval_one(m, reinterpret_cast<uint32_t *>(c.hd_small), ticket, c.stream));
+    rc = await_ticket(c, ticket);
+    if (rc) return rc;
+    *key = reinterpret_cast<const uint32_t *>(c.h_small)[0];
     return MC_OK;
 }
 
@@ -392,10 +412,10 @@ int mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_se
     DevCtx &c = *g_ctx[0];
     std::lock_guard<std::mutex> lk(c.mu);
     CU(cudaSetDevice(c.device));
-    uint32_t *d_out = reinterpret_cast<uint32_t *>(c.d_small);
-    CU(launch_showdown(a, d_out, c.stream));
-    CU(cudaMemcpyAsync(c.h_small, c.d_small, 20 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaStreamSynchronize(c.stream));
+    const uint32_t ticket = ++c.ticket;
+    CU(launch_showdown(a, reinterpret_cast<uint32_t *>(c.hd_small), ticket, c.stream));   // seats by parameter, result into mapped host memory
+    rc = await_ticket(c, ticket);
+    if (rc) return rc;
     const uint32_t *h = reinterpret_cast<const uint32_t *>(c.h_small);
     for (int s = 0; s < n_seats; s++) { if (keys) keys[s] = h[s]; if (group_of) group_of[s] = (int32_t)h[10 + s]; }
     if (n_groups) *n_groups = (int32_t)h[19];

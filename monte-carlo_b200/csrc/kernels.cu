@@ -296,7 +296,7 @@ cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_c
 // ---------------------------------------------------------------------------------------------------
 // single showdown: one warp, lane s = seat s (end-game ranking + group-winners, gameplay.clj:118-132)
 // ---------------------------------------------------------------------------------------------------
-__global__ void showdown_kernel(const __grid_constant__ EquityArgs a, uint32_t *__restrict__ out) {
+__global__ void showdown_kernel(const __grid_constant__ EquityArgs a, uint32_t *__restrict__ out, uint32_t ticket) {
     const int lane = threadIdx.x;
     const bool live = lane < a.n_seats;
     const uint64_t m = live ? (a.board | a.hole[lane]) : 0ull;
@@ -319,9 +319,24 @@ __global__ void showdown_kernel(const __grid_constant__ EquityArgs a, uint32_t *
         out[10 + lane] = (uint32_t)above;
     }
     if (lane == 0) { out[9] = winners; out[19] = n_groups; }
+    // `out` may be mapped host memory that the host polls: results first, then the ticket
+    __threadfence_system();
+    __syncwarp();
+    if (lane == 0) *reinterpret_cast<volatile uint32_t *>(out + SMALL_TICKET_WORD) = ticket;
 }
-cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, cudaStream_t st) {
-    showdown_kernel<<<1, 32, 0, st>>>(a, d_out);
+cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, uint32_t ticket, cudaStream_t st) {
+    showdown_kernel<<<1, 32, 0, st>>>(a, d_out, ticket);
+    return cudaGetLastError();
+}
+
+// one hand, mask by kernel parameter (evaluator / player->hand-value for a single call of the host)
+__global__ void eval_one_kernel(uint64_t m, uint32_t *__restrict__ out, uint32_t ticket) {
+    out[0] = k1_key<K1_NIBBLE_FLO>(m, nullptr, nullptr);
+    __threadfence_system();
+    *reinterpret_cast<volatile uint32_t *>(out + SMALL_TICKET_WORD) = ticket;
+}
+cudaError_t launch_eval_one(uint64_t mask, uint32_t *d_out, uint32_t ticket, cudaStream_t st) {
+    eval_one_kernel<<<1, 1, 0, st>>>(mask, d_out, ticket);
     return cudaGetLastError();
 }
 

@@ -33,7 +33,12 @@ struct EquityArgs {
 };
 // one warp: keys per seat, winner bitmask, tie-group index per seat, number of groups
 // d_out: uint32 keys[9], uint32 winners, int32 group_of[9], int32 n_groups  (20 words)
-cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, cudaStream_t st);
+// d_out of these two may be device-mapped pinned host memory: after the results the kernel writes `ticket` into
+// 32-bit word SMALL_TICKET_WORD of d_out (system-scope fence in between), so the host can poll instead of
+// synchronising the stream
+constexpr int SMALL_TICKET_WORD = 126;           // last 64-bit word of the 64-word scratch: no copy of counts ever lands there
+cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, uint32_t ticket, cudaStream_t st);
+cudaError_t launch_eval_one(uint64_t mask, uint32_t *d_out, uint32_t ticket, cudaStream_t st);
 
 // preflop matrix: matchup list = (hole_a, hole_b, cell index, weight); each block takes matchups
 struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weight; };
