@@ -117,7 +117,7 @@ int upload_tables(DevCtx &c) {
     const size_t off_sb = (off_nib + T.nib_keys.size() * sizeof(uint32_t) + 255) & ~(size_t)255;
     const size_t total = off_sb + SB_BYTES;
     std::vector<unsigned char> sblob;
-    const std::string err = ht_build_stream_blob(T, &sblob);
+    const std::string err = ht_build_stream_blob(T, &sblob, &c.tb.stream_hash);
     if (!err.empty()) return fail(MC_ERR_CUDA, "stream blob construction failed: " + err);
     CU(cudaMalloc(&c.d_tables, total));
     unsigned char *base = static_cast<unsigned char *>(c.d_tables);
@@ -201,14 +201,14 @@ int current_tables(DeviceInfo *di, const DeviceTables **tb) {
 
 // K1 dispatch.  key_format: 0 nibble (auto: hash kernel for large aligned batches, else the rank-set-table kernel),
 // 1 packed, 2 nibble via FLO loops, 3 nibble via the rank-set table, 4 nibble via the hash tables (A/B variants)
-constexpr size_t K1_HASH_MIN = (size_t)1 << 21;     // below this the 212 KB table staging per block outweighs the gain
+constexpr size_t K1_HASH_MIN = (size_t)1 << 21;     // below this the 184 KB table staging per block outweighs the gain
 cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, const DeviceInfo &di,
                       const DeviceTables *tb, cudaStream_t st) {
     const bool aligned = ((reinterpret_cast<uintptr_t>(d_masks) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d_keys) & 7) == 0);
     const bool can_hash = tb && tb->d_stream_blob && aligned;
     if (key_format == 4 || (key_format == 0 && can_hash && n >= K1_HASH_MIN)) {
         if (!can_hash) return cudaErrorInvalidValue;
-        return launch_eval7_stream_hash(d_masks, n, d_keys, tb->d_stream_blob, di, st);
+        return launch_eval7_stream_hash(d_masks, n, d_keys, tb->d_stream_blob, tb->stream_hash, di, st);
     }
     const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
     return launch_eval7_stream(d_masks, n, d_keys, mode, di, st);

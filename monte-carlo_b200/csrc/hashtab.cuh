@@ -59,23 +59,36 @@ MCP_HD uint32_t ht_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi,
 }
 
 // ---- K1 layout ("stream blob"): everything the streaming kernel needs, in one shared-memory image ------------
-// [0, 64 KB)   256 rows of 256 B, row r = byte value r of a 16-bit rank set (a suit lane of the card mask, or a
-//              rank-count bit plane taken over the four lanes, which is how eval7_stream_hash_kernel reads it):
-//                  first half   TL[r] replicated for the 32 lanes (bank == lane: conflict-free for any mix of r);
-//                               TL[r] = sum of RKM[rank] over the bits of r read as ranks 0..7 (only r % 4 == 0 occur)
-//                  second half  TH[r] likewise for ranks 8..15 (only r < 128 occur)
-//              the halves that can never be addressed hold the nibble keys (first halves of rows r % 4 != 0, 32 keys
-//              each) and the flush table (second halves of rows r >= 128, 64 u16 each)
-// [64 KB, +16 KB)  D as in HashBlob
-// [80 KB, ...)     V', same slots as HashBlob::V but holding the BYTE ADDRESS (< 65536) of the hand's nibble key
-// t is linear in the cards, so with count = c0 + 2*c1 + 4*c2 per rank, t = T(c0) + 2*T(c1) + 4*T(c2): a 7-card hand
-// without quads costs 4 conflict-free loads (t), D, V' and the key itself.
-constexpr uint32_t SB_ROWS_BYTES = 65536;
-constexpr uint32_t SB_D_OFF = SB_ROWS_BYTES;
+// The streaming kernel does not sum per-card keys.  It adds the four suit lanes of the mask into per-rank count bit
+// planes (count = c0 + 2*c1 + 4*c2, sh_planes) and hashes the planes themselves: (c0, c1, c2) IS the rank multiset,
+// so u = c0 | c1 << 16 (plus the rare quads plane c2) is an injective 32-bit name of it and two multiplications
+// give the two hash words -- no table is read before the displacement:
+//     t = u * m1 + c2 * m3        slot   = (t >> 16) + D[bucket]
+//     b = u * m2 + c2 * m4        bucket = b >> 19
+// [SB_KEY_OFF, +20 KB)  the 4,892 nibble keys, dense (ascending)
+// [SB_F_OFF,   +16 KB)  flush table: u16 byte address of the key, by (flush lane >> 2)
+// [SB_D_OFF,   +16 KB)  D' = 2 * displacement (in bytes of V'), by bucket
+// [SB_V_OFF,   ...)     V', HT_SLOTS u16: byte address of the hand's nibble key
+// so a 7-card hand costs three data-dependent loads (D', V', key), plus the flush entry when one lane holds >= 5.
+struct StreamHash { uint32_t m1, m2, m3, m4; };
+constexpr uint32_t SB_KEY_OFF = 0;
+constexpr uint32_t SB_F_OFF = 20480;
+constexpr uint32_t SB_D_OFF = SB_F_OFF + HT_FLUSH * 2;
 constexpr uint32_t SB_V_OFF = SB_D_OFF + HT_BUCKETS * 2;
 constexpr uint32_t SB_BYTES = SB_V_OFF + HT_SLOTS * 2;
-static_assert(SB_BYTES % 16 == 0, "stream blob is copied with 16-byte loads");
-MCP_HD uint32_t sb_key_addr(uint32_t dense) { const uint32_t f = dense >> 5; return ((f / 3u) * 4u + f % 3u + 1u) * 256u + (dense & 31u) * 4u; }
-MCP_HD uint32_t sb_flush_addr(uint32_t fi) { return (128u + (fi >> 6)) * 256u + 128u + (fi & 63u) * 2u; }
+static_assert(SB_BYTES % 16 == 0, "stream blob is copied in 16-byte units");
+MCP_HD uint32_t sb_key_addr(uint32_t dense) { return SB_KEY_OFF + 4u * dense; }
+MCP_HD uint32_t sb_flush_addr(uint32_t fi) { return SB_F_OFF + 2u * fi; }
+// rank-count bit planes of a card mask (carry-save addition of the four 16-bit suit lanes); low 16 bits valid
+MCP_HD void sh_planes(uint32_t lo, uint32_t hi, uint32_t *c0, uint32_t *c1, uint32_t *c2) {
+    const uint32_t x = lo ^ hi, y = lo & hi, xs = x >> 16, ys = y >> 16;
+    *c0 = (x ^ xs) & 0xFFFFu;
+    *c1 = ((x & xs) ^ y ^ ys) & 0xFFFFu;
+    *c2 = y & ys;
+}
+MCP_HD uint32_t sh_t(uint32_t c0, uint32_t c1, uint32_t c2, const StreamHash &S) { return (c0 | c1 << 16) * S.m1 + c2 * S.m3; }
+MCP_HD uint32_t sh_b(uint32_t c0, uint32_t c1, uint32_t c2, const StreamHash &S) { return (c0 | c1 << 16) * S.m2 + c2 * S.m4; }
+MCP_HD uint32_t sh_bucket(uint32_t b) { return b >> 19; }
+static_assert(HT_BUCKETS == 1 << 13, "sh_bucket takes the top 13 bits");
 
 }  // namespace mcp

@@ -120,35 +120,69 @@ inline std::string ht_build(const std::vector<HashRep> &reps, const std::vector<
     return "";
 }
 
-// the shared-memory image of the streaming kernel (layout: hashtab.cuh "K1 layout")
-inline std::string ht_build_stream_blob(const HashTables &T, std::vector<unsigned char> *out) {
+// the shared-memory image of the streaming kernel (layout and hash: hashtab.cuh "K1 layout").  The class of every
+// rank multiset is read from the tables of T; this only searches multipliers and lays out a second
+// hash-and-displace table over the plane names of the multisets.
+inline std::string ht_build_stream_blob(const HashTables &T, std::vector<unsigned char> *out, StreamHash *S) {
     out->assign(SB_BYTES, 0);
     unsigned char *B = out->data();
     auto put32 = [&](uint32_t addr, uint32_t v) { std::memcpy(B + addr, &v, 4); };
     auto put16 = [&](uint32_t addr, uint16_t v) { std::memcpy(B + addr, &v, 2); };
-    if (T.nib_keys.size() > 192u * 32u) return "too many classes for the key fragments";
-    for (uint32_t r = 0; r < 256; r++) {
-        uint32_t tl = 0, th = 0;
-        for (int k = 0; k < 8; k++) if ((r >> k) & 1u) { tl += T.card[k].rk; th += T.card[8 + k].rk; }
-        for (uint32_t lane = 0; lane < 32; lane++) {
-            if (r % 4 == 0) put32(r * 256 + lane * 4, tl);
-            if (r < 128) put32(r * 256 + 128 + lane * 4, th);
-        }
-    }
+    if (sb_key_addr((uint32_t)T.nib_keys.size()) > SB_F_OFF) return "too many classes for the key region";
     for (size_t c = 0; c < T.nib_keys.size(); c++) put32(sb_key_addr((uint32_t)c), T.nib_keys[c]);
     auto addr_of_code = [&](uint16_t code) { return (uint16_t)sb_key_addr(T.cat_base[code >> 12] + (code & 0xFFFu)); };
     for (uint32_t fi = 0; fi < (uint32_t)HT_FLUSH; fi++) {
         const int n = __builtin_popcount(fi);
         if (n >= 5 && n <= 7) put16(sb_flush_addr(fi), addr_of_code(T.blob.F[fi]));
     }
-    std::memcpy(B + SB_D_OFF, T.blob.D, sizeof T.blob.D);
-    // V': only occupied slots are meaningful; an empty slot keeps address 0 (never read for a valid hand)
-    std::vector<char> occupied(HT_SLOTS, 0);
+    struct Item { uint32_t c0, c1, c2; uint16_t addr; };
+    std::vector<Item> items;
     std::vector<HashRep> reps;
     ht_representatives(T.mul, &reps);
-    for (auto &h : reps) if (h.flush_index == 0xFFFFFFFFu) occupied[ht_slot(h.t, T.blob.D[ht_bucket(h.t)])] = 1;
-    for (uint32_t s = 0; s < (uint32_t)HT_SLOTS; s++) if (occupied[s]) put16(SB_V_OFF + 2 * s, addr_of_code(T.blob.V[s]));
-    return "";
+    for (auto &h : reps) {
+        if (h.flush_index != 0xFFFFFFFFu) continue;
+        Item it;
+        sh_planes((uint32_t)h.mask, (uint32_t)(h.mask >> 32), &it.c0, &it.c1, &it.c2);
+        it.addr = addr_of_code(T.blob.V[ht_slot(h.t, T.blob.D[ht_bucket(h.t)])]);
+        items.push_back(it);
+    }
+    uint64_t rng = 0x9E3779B97F4A7C15ull;                     // splitmix64: a fixed sequence of odd multipliers
+    auto next_odd = [&]() { rng += 0x9E3779B97F4A7C15ull; uint64_t z = rng; z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+                            z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31; return (uint32_t)(z >> 32) | 1u; };
+    for (int attempt = 0; attempt < 256; attempt++) {
+        StreamHash H{next_odd(), next_odd(), next_odd(), next_odd()};
+        std::vector<std::vector<std::pair<uint32_t, uint16_t>>> bucket(HT_BUCKETS);     // (t >> 16, key address)
+        for (auto &it : items) bucket[sh_bucket(sh_b(it.c0, it.c1, it.c2, H))].push_back({sh_t(it.c0, it.c1, it.c2, H) >> 16, it.addr});
+        std::vector<int> order(HT_BUCKETS);
+        for (int i = 0; i < HT_BUCKETS; i++) order[i] = i;
+        std::sort(order.begin(), order.end(), [&](int a, int b) { return bucket[a].size() != bucket[b].size() ? bucket[a].size() > bucket[b].size() : a < b; });
+        std::vector<char> used(HT_SLOTS, 0);
+        std::vector<uint16_t> D(HT_BUCKETS, 0), V(HT_SLOTS, 0);
+        bool ok = true;
+        for (int b : order) {
+            auto &its = bucket[b];
+            if (its.empty()) break;
+            for (size_t i = 0; i < its.size() && ok; i++)
+                for (size_t j = i + 1; j < its.size(); j++) if (its[i].first == its[j].first) { ok = false; break; }
+            if (!ok) break;
+            uint32_t d = 0;
+            for (; d <= (uint32_t)HT_MAX_DISP; d++) {
+                bool fits = true;
+                for (auto &it : its) if (used[it.first + d]) { fits = false; break; }
+                if (fits) break;
+            }
+            if (d > (uint32_t)HT_MAX_DISP) { ok = false; break; }
+            D[b] = (uint16_t)(2u * d);                                            // D' = byte displacement
+            for (auto &it : its) { used[it.first + d] = 1; V[it.first + d] = it.second; }
+        }
+        if (!ok) continue;
+        // an empty slot keeps address 0 (a valid key address; never read for a valid hand)
+        std::memcpy(B + SB_D_OFF, D.data(), HT_BUCKETS * 2);
+        std::memcpy(B + SB_V_OFF, V.data(), HT_SLOTS * 2);
+        *S = H;
+        return "";
+    }
+    return "no multiplier set gave a displacement table for the streaming hash";
 }
 
 constexpr uint32_t HT_MUL_CANDIDATES[] = {0x165667B1u, 0x27D4EB2Fu, 0x85EBCA6Bu, 0xC2B2AE35u, 0x9E3779B1u};

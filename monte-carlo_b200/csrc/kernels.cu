@@ -106,12 +106,14 @@ static cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K1 v4: streaming evaluation through the additive-key / perfect-hash tables (hashtab.cuh "K1 layout").
-// A valid 7-card hand of the 52-card deck costs four conflict-free byte-table loads (one PRMT each builds the
-// address: row = a byte of a rank-count bit plane, column = the lane), the displacement, the slot and the key; the
-// ALU only adds the suit lanes into count planes, sums, finds a flush lane and checks validity.  Anything else
-// (quads, 5/6 cards, the tests' rank 1, invalid masks) is redone by k1h_general behind one divergent branch per
-// loop iteration; inputs are software-pipelined one iteration ahead.
+// K1 v5: streaming evaluation by hashing the rank-count bit planes (hashtab.cuh "K1 layout").
+// The four suit lanes of the mask are added carry-save into per-rank count planes (7 logic ops); the planes ARE
+// the rank multiset, so two multiplications of u = c0 | c1 << 16 (plus the rare quads plane) give bucket and slot
+// with no table read before the displacement.  A 7-card hand of the 52-card deck costs three data-dependent
+// shared loads (D', V', key) plus the flush entry; shifts and address arithmetic run on the FMA pipe (IMAD,
+// IMAD.HI) and the suit counts on the XU pipe (POPC), because ALU and the l1tex data pipe are the busy ones.
+// Anything else (5/6 cards, the tests' rank 1, invalid masks) is redone by the bit-plane evaluator of eval.cuh
+// behind one divergent branch per loop iteration; inputs are software-pipelined one iteration ahead.
 // ---------------------------------------------------------------------------------------------------
 constexpr int K1H_THREADS = 1024;
 
@@ -119,60 +121,51 @@ constexpr int K1H_THREADS = 1024;
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
 __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
 
-// The common case: a 7-card hand of the 52-card deck in which no rank appears four times.  `odd` is non-zero
-// for everything else (quads plane, bits outside the deck, card count != 7); such a hand is redone by
-// k1h_general.  sb32 = shared address of the stream blob, lane4 = 4 * lane.
-__device__ __forceinline__ uint32_t k1h_fast(uint64_t m, uint32_t sb32, uint32_t lane4, uint32_t &odd) {
+// The key of a 7-card hand of the 52-card deck; `odd` is non-zero for every other mask (bits outside the deck,
+// card count != 7), whose result is then meaningless but whose loads all stay inside the tables.
+// sb32 = shared address of the stream blob.
+__device__ __forceinline__ uint32_t k1h_fast(uint64_t m, uint32_t sb32, const StreamHash &S, uint32_t &odd) {
     const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
-    // per-rank card counts over the four suit lanes as bit planes (carry-save): count = c0 + 2*c1 + 4*c2, so
-    // t = sum of count * RKM[rank] takes four byte-table loads (two bytes of c0, two of c1) instead of eight
+    // per-rank card counts over the four suit lanes as bit planes: count = c0 + 2*c1 + 4*c2 (sh_planes)
     const uint32_t x = lo ^ hi, y = lo & hi;                   // per lane pair: sum bit, carry bit
-    const uint32_t xs = __umulhi(x, 65536u), ys = __umulhi(y, 65536u);   // x >> 16 on the (idle) FMA pipe: the ALU pipe is the busy one
-    const uint32_t c0 = x ^ xs;                                // only the low 16 bits of the planes are read
-    const uint32_t c1 = (x & xs) ^ y ^ ys;
-    const uint32_t t = (lds_u32(sb32 + __byte_perm(c0, lane4, 0x5504)) + lds_u32(sb32 + 128u + __byte_perm(c0, lane4, 0x5514))) +
-                       2u * (lds_u32(sb32 + __byte_perm(c1, lane4, 0x5504)) + lds_u32(sb32 + 128u + __byte_perm(c1, lane4, 0x5514)));
-    // flush lane: only the word holding >= 5 cards can contain it
+    const uint32_t xs = __umulhi(x, 65536u), ys = __umulhi(y, 65536u);   // >> 16 on the FMA pipe
+    const uint32_t c0 = x ^ xs;
+    uint32_t c1;
+    asm("lop3.b32 %0, %1, %2, %3, 0x6A;" : "=r"(c1) : "r"(x), "r"(xs), "r"(y));   // (x & xs) ^ y in one LOP3
+    c1 ^= ys;
+    const uint32_t c2 = y & ys;                                // quads plane (ys has no high half)
+    const uint32_t u = __byte_perm(c0, c1, 0x5410);            // low halves: c0 | c1 << 16
+    const uint32_t t = u * S.m1 + c2 * S.m3;
+    const uint32_t b = u * S.m2 + c2 * S.m4;
+    // flush lane: only the word holding >= 5 cards can contain it (POPC runs on the XU pipe, cheaper here than selects)
     const int p01 = __popc(lo), p23 = __popc(hi);
-    const bool up = p23 >= 5;
-    const uint32_t w = up ? hi : lo;
-    const int pw = up ? p23 : p01;
-    const uint32_t wl = w & 0xFFFFu, wh = w >> 16;
-    const int pl = __popc(wl), ph = pw - pl;
-    const uint32_t fm = pl >= 5 ? wl : (ph >= 5 ? wh : 0u);
-    odd = (y & ys) | ((lo | hi) & 0x80038003u) | (uint32_t)(p01 + p23 - 7);      // ys has no high half, so y & ys is the quads plane
-    const uint32_t d = lds_u16(sb32 + SB_D_OFF + (t & 0x3FFEu));
-    uint32_t ka = lds_u16(sb32 + SB_V_OFF + 2u * ((t >> 16) + d));
-    // masked: whatever the mask holds, the address stays inside the table
-    if (fm) ka = lds_u16(sb32 + 0x8080u + (fm & 0x7F00u) + ((fm >> 1) & 0x7Eu));      // == sb_flush_addr(fm >> 2)
+    const uint32_t w = p23 >= 5 ? hi : lo;
+    const uint32_t wm = w & 0x7FFC7FFCu;                       // rank bits only: the flush address stays inside F for any mask
+    const uint32_t wl = wm & 0xFFFFu;
+    const int pw = __popc(w), pl = __popc(wl);
+    const bool low5 = pl >= 5;
+    const uint32_t fm = low5 ? wl : __umulhi(wm, 65536u);
+    const bool flush = low5 || (pw - pl >= 5);
+    odd = ((lo | hi) & 0x80038003u) | (uint32_t)(p01 + p23 - 7);
+    // D' holds 2 * displacement, so the byte address of the slot is one IMAD: 2 * (t >> 16) + D'[bucket]
+    const uint32_t d2 = lds_u16(sb32 + SB_D_OFF + __umulhi(b, 8192u) * 2u);
+    uint32_t ka = lds_u16(sb32 + SB_V_OFF + (__umulhi(t, 65536u) * 2u + d2));
+    if (flush) ka = lds_u16(sb32 + SB_F_OFF + (fm >> 1));      // == sb_flush_addr(fm >> 2)
     return lds_u32(sb32 + ka);
 }
 
-// any mask: quads, 5/6 cards, the tests' rank 1, invalid masks; also correct for the common case
-__device__ __noinline__ uint32_t k1h_general(uint64_t m, uint32_t sb32, uint32_t lane4) {
+// everything that is not a 7-card hand of the 52-card deck
+__device__ __noinline__ uint32_t k1h_slow(uint64_t m) {
     const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
     const uint32_t n = (uint32_t)(__popc(lo) + __popc(hi));
-    if (n != 7u || ((lo | hi) & 0x80038003u)) {
-        const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
-        return ok ? packed_to_nibble(eval_packed(lo, hi)) : 0xFFFFFFFFu;
-    }
-    uint32_t t = 0, fm = 0;
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const uint32_t w = k < 2 ? lo : hi, lane = (k & 1) ? (w >> 16) : (w & 0xFFFFu);
-        t += lds_u32(sb32 + ((lane & 0xFFu) << 8) + lane4) + lds_u32(sb32 + 128u + (lane & 0xFF00u) + lane4);
-        if (__popc(lane) >= 5) fm = lane;
-    }
-    const uint32_t d = lds_u16(sb32 + SB_D_OFF + (t & 0x3FFEu));
-    uint32_t ka = lds_u16(sb32 + SB_V_OFF + 2u * ((t >> 16) + d));
-    if (fm) ka = lds_u16(sb32 + sb_flush_addr(fm >> 2));
-    return lds_u32(sb32 + ka);
+    const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
+    return ok ? packed_to_nibble(eval_packed(lo, hi)) : 0xFFFFFFFFu;
 }
 
 // one launch covers at most 2^31 hands, so every index fits 32 bits (the launcher cuts longer batches)
 __global__ void __launch_bounds__(K1H_THREADS, 1)
 eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, uint32_t n,
-                         const uint4 *__restrict__ g_blob) {
+                         const uint4 *__restrict__ g_blob, const __grid_constant__ StreamHash S) {
     extern __shared__ __align__(16) unsigned char sb[];
     __shared__ unsigned long long mbar;
     BulkStage stage;
@@ -180,7 +173,6 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
     stage.wait();
     uint32_t sb32 = (uint32_t)__cvta_generic_to_shared(sb);
     asm volatile("" : "+r"(sb32) : : "memory");               // every table load depends on this: none moves above the wait
-    const uint32_t lane4 = (threadIdx.x & 31u) * 4u;
     const uint32_t npair = n >> 1;
     const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);
     uint2 *out = reinterpret_cast<uint2 *>(keys);
@@ -199,15 +191,15 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
             const ulonglong2 nb = __ldcs(in + min(j + 2 * stride, last));
             uint32_t o0, o1, o2, o3;
             uint2 ka, kb;
-            ka.x = k1h_fast(a.x, sb32, lane4, o0);
-            ka.y = k1h_fast(a.y, sb32, lane4, o1);
-            kb.x = k1h_fast(b.x, sb32, lane4, o2);
-            kb.y = k1h_fast(b.y, sb32, lane4, o3);
-            if (o0 | o1 | o2 | o3) {                          // one lane in ~150 per iteration: a single divergent branch
-                if (o0) ka.x = k1h_general(a.x, sb32, lane4);
-                if (o1) ka.y = k1h_general(a.y, sb32, lane4);
-                if (o2) kb.x = k1h_general(b.x, sb32, lane4);
-                if (o3) kb.y = k1h_general(b.y, sb32, lane4);
+            ka.x = k1h_fast(a.x, sb32, S, o0);
+            ka.y = k1h_fast(a.y, sb32, S, o1);
+            kb.x = k1h_fast(b.x, sb32, S, o2);
+            kb.y = k1h_fast(b.y, sb32, S, o3);
+            if (o0 | o1 | o2 | o3) {                          // never for 7-card hands of the deck: one divergent branch
+                if (o0) ka.x = k1h_slow(a.x);
+                if (o1) ka.y = k1h_slow(a.y);
+                if (o2) kb.x = k1h_slow(b.x);
+                if (o3) kb.y = k1h_slow(b.y);
             }
             __stcs(out + i, ka);
             if (j < npair) __stcs(out + j, kb);
@@ -215,11 +207,16 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
             b = nb;
         }
     }
-    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) keys[n - 1] = k1h_general(masks[n - 1], sb32, lane4);
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+        const uint64_t m = masks[n - 1];
+        uint32_t o;
+        const uint32_t k = k1h_fast(m, sb32, S, o);
+        keys[n - 1] = o ? k1h_slow(m) : k;
+    }
 }
 
 cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
-                                     const DeviceInfo &di, cudaStream_t st) {
+                                     const StreamHash &S, const DeviceInfo &di, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     cudaError_t e = cudaFuncSetAttribute(eval7_stream_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_BYTES);
     if (e != cudaSuccess) return e;
@@ -229,7 +226,7 @@ cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t
         size_t want = (m + (size_t)K1H_THREADS * 4 - 1) / ((size_t)K1H_THREADS * 4);
         const int grid = (int)(want > (size_t)di.sm_count ? (size_t)di.sm_count : want);
         eval7_stream_hash_kernel<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks + off, d_keys + off, (uint32_t)m,
-                                                                      reinterpret_cast<const uint4 *>(d_stream_blob));
+                                                                      reinterpret_cast<const uint4 *>(d_stream_blob), S);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }

@@ -3,6 +3,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <cuda_runtime.h>
+#include "hashtab.cuh"
 
 namespace mcp {
 
@@ -22,7 +23,7 @@ cudaError_t launch_eval7_stream(const uint64_t *d_masks, size_t n, uint32_t *d_k
                                 const DeviceInfo &di, cudaStream_t st);
 // requires 16-byte aligned masks / 8-byte aligned keys; d_stream_blob = SB_BYTES image (hashtab.cuh "K1 layout")
 cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
-                                     const DeviceInfo &di, cudaStream_t st);
+                                     const StreamHash &S, const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,
                                 const DeviceInfo &di, cudaStream_t st);
 struct EquityArgs {
@@ -44,14 +45,13 @@ cudaError_t launch_eval_one(uint64_t mask, uint32_t *d_out, uint32_t ticket, cud
 struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weight; };
 
 // ---- kernels on the additive-key / perfect-hash evaluator (kernels_hash.cu, hashtab.cuh) ----------------
-struct HashBlob;
-struct CardKey;
 struct CatBase { uint32_t v[10]; };          // dense class index of the first class of each category; v[9] = #classes
 struct DeviceTables {
     const HashBlob *d_blob = nullptr;        // device: D / F / V
     const CardKey *d_card = nullptr;         // device: 64 entries by bit position
     const uint32_t *d_nib = nullptr;         // device: dense class index -> nibble key
     const void *d_stream_blob = nullptr;     // device: shared-memory image of the streaming kernel (K1)
+    StreamHash stream_hash{};                // its multipliers
     const CardKey *h_card = nullptr;         // host copy of d_card
     CatBase cat_base{};
     uint32_t n_classes = 0;

@@ -33,22 +33,21 @@ static int check_hash() {
     }
     if (!err.empty()) { fprintf(stderr, "ht_build: %s\n", err.c_str()); return 1; }
     printf("hash tables: mul=%08x classes=%zu reps=%zu\n", T.mul, T.nib_keys.size(), reps.size());
-    // the shared-memory image of the streaming kernel (K1 v4), read here exactly as k1h_key reads it for lane 5
+    // the shared-memory image of the streaming kernel (K1), read here exactly as k1h_fast reads it
     std::vector<unsigned char> sb;
-    err = mcp::ht_build_stream_blob(T, &sb);
+    mcp::StreamHash SH;
+    err = mcp::ht_build_stream_blob(T, &sb, &SH);
     if (!err.empty()) { fprintf(stderr, "ht_build_stream_blob: %s\n", err.c_str()); return 1; }
+    printf("stream hash multipliers: %08x %08x %08x %08x\n", SH.m1, SH.m2, SH.m3, SH.m4);
     auto rd32 = [&](uint32_t a) { uint32_t v; memcpy(&v, sb.data() + a, 4); return v; };
     auto rd16 = [&](uint32_t a) { uint16_t v; memcpy(&v, sb.data() + a, 2); return (uint32_t)v; };
     auto stream_key = [&](uint64_t m) -> uint32_t {
-        // rank-count bit planes over the four suit lanes, as in k1h_key: count = c0 + 2*c1 + 4*c2
-        const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32), x = lo ^ hi, y = lo & hi, xs = x >> 16, ys = y >> 16;
-        const uint32_t plane[3] = {(x ^ xs) & 0xFFFFu, ((x & xs) ^ y ^ ys) & 0xFFFFu, y & ys & 0xFFFFu};
-        uint32_t t = 0;
-        for (int p = 0; p < 3; p++)
-            t += (rd32((plane[p] & 255u) * 256u + 5 * 4) + rd32((plane[p] >> 8) * 256u + 128 + 5 * 4)) << p;
+        uint32_t c0, c1, c2;
+        mcp::sh_planes((uint32_t)m, (uint32_t)(m >> 32), &c0, &c1, &c2);
+        const uint32_t t = mcp::sh_t(c0, c1, c2, SH), bk = mcp::sh_bucket(mcp::sh_b(c0, c1, c2, SH));
         uint32_t fm = 0;
         for (int s4 = 0; s4 < 4; s4++) { uint32_t lane = (uint32_t)(m >> (16 * s4)) & 0xFFFFu; if (__builtin_popcount(lane) >= 5) fm = lane; }
-        uint32_t ka = rd16(mcp::SB_V_OFF + 2u * ((t >> 16) + rd16(mcp::SB_D_OFF + (t & 0x3FFEu))));
+        uint32_t ka = rd16(mcp::SB_V_OFF + 2u * (t >> 16) + rd16(mcp::SB_D_OFF + 2u * bk));   // D' is in bytes
         if (fm) ka = rd16(mcp::sb_flush_addr(fm >> 2));
         return rd32(ka);
     };
