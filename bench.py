@@ -30,8 +30,8 @@ E2E_LOG2 = 26                    # hands per GPU per step through the host-buffe
 ALGO_BYTES_PER_EVAL = 12         # 8 B mask in + 4 B key out
 # thread-level instructions per unit.  SURVEY 8d declared 64 / 70 / 140 / 1024 and allows lowering them "with a SASS
 # count to justify it": these are the executed warp-instructions per unit that ncu measured for the current kernels
-# (profiles/r01_r_k1_v4_ncu_full.txt, profiles/r01_o_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
-OPS = {"eval": 59, "enum": 69, "board2": 78, "mc9": 702}
+# (profiles/r01_v_k1_v5_ncu_full.txt, profiles/r01_o_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
+OPS = {"eval": 46, "enum": 69, "board2": 78, "mc9": 702}
 METRIC = "7-card evals/s"
 
 
@@ -242,7 +242,7 @@ def run_ours(args):
             raise SystemExit("K1 keys differ from the oracle: refusing to report a number")
     variants = {}
     for name, fmt in (("packed_key_bitplane", E.KEY_PACKED), ("nibble_flo_bitplane", E.KEY_NIBBLE_FLO),
-                      ("nibble_rankset_table_v2", E.KEY_NIBBLE_TABLE), ("nibble_hash_v4", E.KEY_NIBBLE_HASH)):
+                      ("nibble_rankset_table_v2", E.KEY_NIBBLE_TABLE), ("nibble_plane_hash_v5", E.KEY_NIBBLE_HASH)):
         v_ms = timed_region(torch, dist, world, lambda: k1_step(fmt), max(2, args.steps // 2), 1)
         variants[name] = world * n * max(2, args.steps // 2) / (v_ms * 1e-3)
 

@@ -116,6 +116,7 @@ static cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys
 // behind one divergent branch per loop iteration; inputs are software-pipelined one iteration ahead.
 // ---------------------------------------------------------------------------------------------------
 constexpr int K1H_THREADS = 1024;
+constexpr int K1H_RING_DEFAULT = 6;           // measured on a B200: 3: 482, 4: 508, 5: 515, 6: 532, 8: 525 G evals/s
 
 // shared-space loads by 32-bit address: the tables never change after staging, so these are plain (movable) asm
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
@@ -163,6 +164,7 @@ __device__ __noinline__ uint32_t k1h_slow(uint64_t m) {
 }
 
 // one launch covers at most 2^31 hands, so every index fits 32 bits (the launcher cuts longer batches)
+template <int K1H_RING>
 __global__ void __launch_bounds__(K1H_THREADS, 1)
 eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, uint32_t n,
                          const uint4 *__restrict__ g_blob, const __grid_constant__ StreamHash S) {
@@ -177,34 +179,33 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
     const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);
     uint2 *out = reinterpret_cast<uint2 *>(keys);
     const uint32_t stride = gridDim.x * blockDim.x;
-    // software pipeline: the next iteration's 32 bytes are requested before this iteration's four hands are
-    // evaluated, so every thread keeps loads in flight while it works (32 warps x 32 B per SM, issued only
-    // between evaluations, is less than bandwidth x latency).  Prefetch indices are clamped, not predicated.
+    // software pipeline: a thread evaluates two hands (16 bytes) per step and keeps the loads of its next RING - 1
+    // steps in flight (80 B per thread, 80 KB per SM at RING = 6: HBM bandwidth x latency needs well over 32 KB
+    // per SM).  The ring is unrolled so that it stays in registers; prefetch indices are clamped, not predicated.
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < npair) {
         const uint32_t last = npair - 1u;
-        ulonglong2 a = __ldcs(in + i);
-        ulonglong2 b = __ldcs(in + min(i + stride, last));
-        for (; i < npair; i += 2 * stride) {
-            const uint32_t j = i + stride;
-            const ulonglong2 na = __ldcs(in + min(j + stride, last));
-            const ulonglong2 nb = __ldcs(in + min(j + 2 * stride, last));
-            uint32_t o0, o1, o2, o3;
-            uint2 ka, kb;
-            ka.x = k1h_fast(a.x, sb32, S, o0);
-            ka.y = k1h_fast(a.y, sb32, S, o1);
-            kb.x = k1h_fast(b.x, sb32, S, o2);
-            kb.y = k1h_fast(b.y, sb32, S, o3);
-            if (o0 | o1 | o2 | o3) {                          // never for 7-card hands of the deck: one divergent branch
-                if (o0) ka.x = k1h_slow(a.x);
-                if (o1) ka.y = k1h_slow(a.y);
-                if (o2) kb.x = k1h_slow(b.x);
-                if (o3) kb.y = k1h_slow(b.y);
+        constexpr int RING = K1H_RING;                        // RING - 1 steps in flight
+        ulonglong2 q[RING];
+#pragma unroll
+        for (int k = 0; k < RING - 1; k++) q[k] = __ldcs(in + min(i + k * stride, last));
+        while (true) {
+#pragma unroll
+            for (int k = 0; k < RING; k++) {
+                q[(k + RING - 1) % RING] = __ldcs(in + min(i + (RING - 1) * stride, last));
+                uint32_t o0, o1;
+                uint2 kk;
+                kk.x = k1h_fast(q[k].x, sb32, S, o0);
+                kk.y = k1h_fast(q[k].y, sb32, S, o1);
+                if (o0 | o1) {                                // never for 7-card hands of the deck: one divergent branch
+                    if (o0) kk.x = k1h_slow(q[k].x);
+                    if (o1) kk.y = k1h_slow(q[k].y);
+                }
+                __stcs(out + i, kk);
+                i += stride;
+                if (i >= npair) break;
             }
-            __stcs(out + i, ka);
-            if (j < npair) __stcs(out + j, kb);
-            a = na;
-            b = nb;
+            if (i >= npair) break;
         }
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
@@ -218,15 +219,16 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
 cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
                                      const StreamHash &S, const DeviceInfo &di, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(eval7_stream_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_BYTES);
+    auto kern = eval7_stream_hash_kernel<K1H_RING_DEFAULT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_BYTES);
     if (e != cudaSuccess) return e;
     constexpr size_t CHUNK = (size_t)1 << 30;                 // hands per launch: even, so every chunk keeps the alignment
     for (size_t off = 0; off < n; off += CHUNK) {
         const size_t m = n - off < CHUNK ? n - off : CHUNK;
         size_t want = (m + (size_t)K1H_THREADS * 4 - 1) / ((size_t)K1H_THREADS * 4);
         const int grid = (int)(want > (size_t)di.sm_count ? (size_t)di.sm_count : want);
-        eval7_stream_hash_kernel<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks + off, d_keys + off, (uint32_t)m,
-                                                                      reinterpret_cast<const uint4 *>(d_stream_blob), S);
+        kern<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks + off, d_keys + off, (uint32_t)m,
+                                                  reinterpret_cast<const uint4 *>(d_stream_blob), S);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
