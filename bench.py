@@ -81,8 +81,18 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def use_all_host_threads(oracle):
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU baseline is meant to use all the host cores"""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    oracle.lib().orc_set_threads(n)
+
+
 def cpu_port_baseline(oracle, seconds_target=12.0):
     """the reference's algorithm (literal port, all host threads) on a bounded sample of the K1 workload"""
+    use_all_host_threads(oracle)
     cores = oracle.lib().orc_max_threads()
     probe = oracle.random_hands(SEED, 0, 4000 * cores)
     t = time.perf_counter()
@@ -103,6 +113,7 @@ def run_reference(args):
     if rank != 0:
         return
     import oracle_lib as oracle
+    use_all_host_threads(oracle)
     cores = oracle.lib().orc_max_threads()
     probe = oracle.random_hands(SEED, 0, 2000 * cores)
     t = time.perf_counter()

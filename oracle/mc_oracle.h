@@ -114,6 +114,7 @@ int  orc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask,
 int  orc_preflop_cell(int class_a, int class_b, int threads, int64_t wtl[3]);
 
 int  orc_max_threads(void);
+void orc_set_threads(int threads);   /* overrides OMP_NUM_THREADS for the calls that follow */
 
 #ifdef __cplusplus
 }

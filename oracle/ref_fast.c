@@ -28,6 +28,14 @@ int orc_max_threads(void) {
     return 1;
 #endif
 }
+/* the launcher (torchrun) exports OMP_NUM_THREADS=1; the timed CPU baseline wants every host core it may use */
+void orc_set_threads(int t) {
+#ifdef _OPENMP
+    if (t > 0) omp_set_num_threads(t);
+#else
+    (void)t;
+#endif
+}
 static int use_threads(int t) { int m = orc_max_threads(); return (t <= 0 || t > m) ? m : t; }
 
 static uint32_t pack_key(int cat, const int *r) {
