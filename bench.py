@@ -272,6 +272,18 @@ def run_ours(args):
     e2e_value = world * ne * e2e_steps / (e2e_ms * 1e-3)
     if rank == 0 and not torch.equal(h_keys[:check_n], keys[:check_n].cpu()):
         raise SystemExit("e2e keys differ from the device-resident run")
+    # the host link alone: the same pinned buffers copied with nothing else running (what bounds e2e)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    masks[:ne].copy_(h_masks, non_blocking=True)
+    torch.cuda.synchronize()
+    ev[0].record(); masks[:ne].copy_(h_masks, non_blocking=True); ev[1].record()
+    ev[2].record(); h_keys.copy_(keys[:ne], non_blocking=True); ev[3].record()
+    torch.cuda.synchronize()
+    h2d_alone = 8 * ne / (ev[0].elapsed_time(ev[1]) * 1e-3) / 1e9
+    d2h_alone = 4 * ne / (ev[2].elapsed_time(ev[3]) * 1e-3) / 1e9
+    link = {"h2d_alone_gbs": h2d_alone, "d2h_alone_gbs": d2h_alone, "h2d_in_e2e_gbs": 8 * e2e_value / world / 1e9,
+            "d2h_in_e2e_gbs": 4 * e2e_value / world / 1e9, "frac_of_h2d_alone": 8 * e2e_value / world / 1e9 / h2d_alone,
+            "note": "e2e moves 12 B per hand over the host link, both directions at once; it is bound by the H2D direction"}
     del masks, keys
 
     # ---- other BASELINE configs --------------------------------------------------------------------
@@ -427,7 +439,8 @@ def run_ours(args):
                          "kernel": "eval7_stream_hash_kernel", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
                          "int_issue_frac": (value / world) * OPS["eval"] / int_peak, "ops_per_eval": OPS["eval"]},
             "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
-                    "hands_per_step": ne, "call": "mc_eval7_batch (pinned host buffers, 3-stage copy/compute pipeline)"},
+                    "hands_per_step": ne, "call": "mc_eval7_batch (pinned host buffers, 3-stage copy/compute pipeline)",
+                    "link": link},
             "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
             "k1_variants_evals_per_s": variants, "workloads": work,
         }
