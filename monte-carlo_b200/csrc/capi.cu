@@ -201,12 +201,13 @@ int current_tables(DeviceInfo *di, const DeviceTables **tb) {
 
 // K1 dispatch.  key_format: 0 nibble (auto: hash kernel for large aligned batches, else the rank-set-table kernel),
 // 1 packed, 2 nibble via FLO loops, 3 nibble via the rank-set table, 4 nibble via the hash tables (A/B variants)
-constexpr size_t K1_HASH_MIN = (size_t)1 << 21;     // below this the 184 KB table staging per block outweighs the gain
+// the plane-hash kernel serves every aligned batch: measured (tools/k1_crossover.py) it wins at every size (6 us floor:
+// 184 KB staged by TMA; the rank-set-table kernel computes its 64 KB table in every block, 12 us)
 cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, const DeviceInfo &di,
                       const DeviceTables *tb, cudaStream_t st) {
     const bool aligned = ((reinterpret_cast<uintptr_t>(d_masks) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d_keys) & 7) == 0);
     const bool can_hash = tb && tb->d_stream_blob && aligned;
-    if (key_format == 4 || (key_format == 0 && can_hash && n >= K1_HASH_MIN)) {
+    if (key_format == 4 || (key_format == 0 && can_hash)) {
         if (!can_hash) return cudaErrorInvalidValue;
         return launch_eval7_stream_hash(d_masks, n, d_keys, tb->d_stream_blob, tb->stream_hash, di, st);
     }
