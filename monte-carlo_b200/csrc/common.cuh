@@ -74,6 +74,19 @@ struct BulkStage {
     }
 };
 
+// Loads from a staged (read-only) shared-memory table by 32-bit shared address.  Plain asm, so the compiler may
+// schedule them freely; u16 entries arrive zero-extended in a full register (a C++ uint16_t load is kept as a
+// 16-bit value and merged / masked with extra PRMT and LOP3 around every select or compare).
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+// shared address of a table, to be taken AFTER BulkStage::wait(): every lds_* through it depends on this volatile
+// asm, so none can move above the wait, and the compiler keeps the base in a register instead of rebuilding it
+__device__ __forceinline__ uint32_t staged_table_base(const void *smem_table) {
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(smem_table);
+    asm volatile("" : "+r"(a) : : "memory");
+    return a;
+}
+
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xFFFFFFFFu, v); }
 __device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
 #pragma unroll

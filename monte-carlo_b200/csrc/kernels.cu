@@ -118,9 +118,6 @@ static cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys
 constexpr int K1H_THREADS = 1024;
 constexpr int K1H_RING_DEFAULT = 6;           // measured on a B200: 3: 482, 4: 508, 5: 515, 6: 532, 8: 525 G evals/s
 
-// shared-space loads by 32-bit address: the tables never change after staging, so these are plain (movable) asm
-__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
-__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
 
 // The key of a 7-card hand of the 52-card deck; `odd` is non-zero for every other mask (bits outside the deck,
 // card count != 7), whose result is then meaningless but whose loads all stay inside the tables.
@@ -173,8 +170,7 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
     BulkStage stage;
     stage.start(&mbar, sb, g_blob, SB_BYTES);
     stage.wait();
-    uint32_t sb32 = (uint32_t)__cvta_generic_to_shared(sb);
-    asm volatile("" : "+r"(sb32) : : "memory");               // every table load depends on this: none moves above the wait
+    const uint32_t sb32 = staged_table_base(sb);
     const uint32_t npair = n >> 1;
     const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);
     uint2 *out = reinterpret_cast<uint2 *>(keys);

@@ -104,6 +104,25 @@ struct Tally {
 constexpr int HASH_THREADS = 512;
 constexpr int LIVE_MAX = 56;
 
+// ht_class of hashtab.cuh over a HashBlob staged in shared memory at shared address hb (staged_table_base)
+constexpr uint32_t HB_F = HT_BUCKETS * 2, HB_V = HB_F + HT_FLUSH * 2;
+static_assert(sizeof(HashBlob) == HB_V + HT_SLOTS * 2, "HashBlob is D, F, V back to back");
+__device__ __forceinline__ uint32_t hb_rank_class(uint32_t t, uint32_t hb) {
+    const uint32_t d = lds_u16(hb + (t & 0x3FFEu));                       // D[(t >> 1) & 8191]
+    return lds_u16(hb + HB_V + 2u * ((t >> 16) + d));
+}
+__device__ __forceinline__ uint32_t hb_flush_class(uint32_t lane_ranks, uint32_t hb) { return lds_u16(hb + HB_F + 2u * lane_ranks); }
+__device__ __forceinline__ uint32_t hb_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi, uint32_t hb) {
+    const uint32_t flag = sn & 0x8888u;
+    if (flag) {
+        // flag is exactly one of 0x8, 0x80, 0x800, 0x8000 for <= 9 cards
+        const uint32_t w = (flag & 0x8800u) ? mhi : mlo;                  // suits 2,3 live in the high word
+        const uint32_t lane = (flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu);
+        return hb_flush_class(lane >> 2, hb);
+    }
+    return hb_rank_class(t, hb);
+}
+
 // ---------------------------------------------------------------------------------------------------
 // K3: exhaustive equity over all K-card completions of the board
 // ---------------------------------------------------------------------------------------------------
@@ -131,6 +150,7 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
     if (threadIdx.x < LIVE_MAX) slive[threadIdx.x] = prm.live[threadIdx.x];
     if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
     stage.wait();
+    const uint32_t tbl = staged_table_base(H);
 
     const int n_seats = prm.n_seats, nl = prm.n_live;
     Tally<NS> tl; tl.clear();
@@ -149,8 +169,7 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
             for (int s = 0; s < NS; s++) {
                 key[s] = 0;
                 if (NS == 2 || s < n_seats)
-                    key[s] = ht_class(b.t + prm.h_t[s], b.sn + prm.h_sn[s], b.mlo | prm.h_mlo[s], b.mhi | prm.h_mhi[s],
-                                      H->D, H->F, H->V);
+                    key[s] = hb_class(b.t + prm.h_t[s], b.sn + prm.h_sn[s], b.mlo | prm.h_mlo[s], b.mhi | prm.h_mhi[s], tbl);
             }
             tl.add(key, n_seats);
             w.next(slive, nl);
@@ -228,6 +247,7 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
     fill_binom(sbin);
     if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
     stage.wait();
+    const uint32_t tbl = staged_table_base(H);
     const uint32_t total = cbinom(48, 5);
     const uint32_t per = (total + PF_THREADS - 1) / PF_THREADS;
     for (int mi = blockIdx.x; mi < n_mu; mi += gridDim.x) {
@@ -255,8 +275,8 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
             w.init(lo, 48, sbin, slive, HandState{0, SN_BIAS, 0, 0});
             for (uint32_t i = lo; i < hi; i++) {
                 const HandState b = w.hand();
-                const uint32_t ka = ht_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, H->D, H->F, H->V);
-                const uint32_t kb = ht_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, H->D, H->F, H->V);
+                const uint32_t ka = hb_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, tbl);
+                const uint32_t kb = hb_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, tbl);
                 wa += ka > kb; wb += kb > ka; tie += ka == kb;
                 w.next(slive, 48);
             }
@@ -314,6 +334,7 @@ range_equity_kernel(const Matchup *__restrict__ mus, int n_mu, uint64_t board, u
     fill_binom(sbin);
     if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
     stage.wait();
+    const uint32_t tbl = staged_table_base(H);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint4 *slive = slive_all + warp * LIVE_MAX;
@@ -350,8 +371,8 @@ range_equity_kernel(const Matchup *__restrict__ mus, int n_mu, uint64_t board, u
             w.init(lo, nl, sbin, slive, base);
             for (uint32_t i = lo; i < hi; i++) {
                 const HandState b = w.hand();
-                const uint32_t ka = ht_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, H->D, H->F, H->V);
-                const uint32_t kb = ht_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, H->D, H->F, H->V);
+                const uint32_t ka = hb_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, tbl);
+                const uint32_t kb = hb_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, tbl);
                 ca += ka > kb; cb += kb > ka; ct += ka == kb;
                 w.next(slive, nl);
             }
@@ -430,6 +451,7 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
         scat[c] = make_uint4(c < 10 ? cb.v[c] : 0u, c < 4 ? 1u << (8 * c) : 0u, (c >= 4 && c < 9) ? 1u << (6 * (c - 4)) : 0u, 0u);
     }
     stage.wait();
+    const uint32_t tbl = staged_table_base(H);
 
     uint32_t h[9];
 #pragma unroll
@@ -448,7 +470,7 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
             uint32_t acc_lo = 0, acc_hi = 0, nsum = 0;                // nsum <= 32 * 2^24
             for (uint32_t j = 0; j < len; j++) {
                 const HandState s = w.hand();
-                const uint32_t code = ht_class(s.t, s.sn, s.mlo, s.mhi, H->D, H->F, H->V);
+                const uint32_t code = hb_class(s.t, s.sn, s.mlo, s.mhi, tbl);
                 const uint4 ci = scat[code >> 12];
                 acc_lo += ci.y; acc_hi += ci.z;
                 nsum += snib[ci.x + (code & 0xFFFu)];
@@ -558,6 +580,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     }
     if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
     stage.wait();
+    const uint32_t tbl = staged_table_base(H);
 
     const uint32_t tid4 = 4u * threadIdx.x;
     unsigned char *dk = sdeck + tid4;
@@ -623,10 +646,10 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         for (int q = 0; q < NR; q++) {
             const uint2 e1 = rep_of(card[q]), e2 = rep_of(card[q + NR]);
             const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + e1.y + e2.y;
-            uint32_t k = H->V[ht_slot(t, H->D[ht_bucket(t)])];
+            uint32_t k = hb_rank_class(t, tbl);
             if (sn & 0x8888u) {
                 const uint32_t fm = lb | ((e1.y & cbit) ? (e1.y >> 16) : 0u) | ((e2.y & cbit) ? (e2.y >> 16) : 0u);
-                k = H->F[fm];
+                k = hb_flush_class(fm, tbl);
             }
             key[q] = k;
         }
@@ -635,10 +658,10 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
             key[NR + s] = 0;
             if (s < nf) {
                 const uint32_t t = b.t + prm.h_t[s], sn = b.sn + prm.h_sn[s];
-                uint32_t k = H->V[ht_slot(t, H->D[ht_bucket(t)])];
+                uint32_t k = hb_rank_class(t, tbl);
                 if (sn & 0x8888u) {
                     const uint32_t hw = (cbit & 0x1100u) ? prm.h_mhi[s] : prm.h_mlo[s];
-                    k = H->F[lb | (((cbit & 0x1010u) ? (hw >> 16) : (hw & 0xFFFFu)) >> 2)];
+                    k = hb_flush_class(lb | (((cbit & 0x1010u) ? (hw >> 16) : (hw & 0xFFFFu)) >> 2), tbl);
                 }
                 key[NR + s] = k;
             }
