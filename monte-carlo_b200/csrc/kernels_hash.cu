@@ -107,20 +107,20 @@ constexpr int LIVE_MAX = 56;
 // ht_class of hashtab.cuh over a HashBlob staged in shared memory at shared address hb (staged_table_base)
 constexpr uint32_t HB_F = HT_BUCKETS * 2, HB_V = HB_F + HT_FLUSH * 2;
 static_assert(sizeof(HashBlob) == HB_V + HT_SLOTS * 2, "HashBlob is D, F, V back to back");
-__device__ __forceinline__ uint32_t hb_rank_class(uint32_t t, uint32_t hb) {
+// Branch-free: the displacement is always read; a hand with a flush then reads F instead of V through the SAME load
+// (its address is selected), so the evaluations of several hands / seats overlap instead of being fenced by a
+// divergent branch each.
+__device__ __forceinline__ uint32_t hb_slot_addr(uint32_t t, uint32_t hb) {
     const uint32_t d = lds_u16(hb + (t & 0x3FFEu));                       // D[(t >> 1) & 8191]
-    return lds_u16(hb + HB_V + 2u * ((t >> 16) + d));
+    return hb + HB_V + 2u * ((t >> 16) + d);
 }
-__device__ __forceinline__ uint32_t hb_flush_class(uint32_t lane_ranks, uint32_t hb) { return lds_u16(hb + HB_F + 2u * lane_ranks); }
+__device__ __forceinline__ uint32_t hb_flush_addr(uint32_t lane_ranks, uint32_t hb) { return hb + HB_F + 2u * lane_ranks; }
 __device__ __forceinline__ uint32_t hb_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi, uint32_t hb) {
-    const uint32_t flag = sn & 0x8888u;
-    if (flag) {
-        // flag is exactly one of 0x8, 0x80, 0x800, 0x8000 for <= 9 cards
-        const uint32_t w = (flag & 0x8800u) ? mhi : mlo;                  // suits 2,3 live in the high word
-        const uint32_t lane = (flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu);
-        return hb_flush_class(lane >> 2, hb);
-    }
-    return hb_rank_class(t, hb);
+    const uint32_t flag = sn & 0x8888u;                                   // one of 0x8, 0x80, 0x800, 0x8000 (or 0) for <= 9 cards
+    const uint32_t w = (flag & 0x8800u) ? mhi : mlo;                      // suits 2,3 live in the high word
+    const uint32_t lane = (flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu);
+    const uint32_t va = hb_slot_addr(t, hb), fa = hb_flush_addr(lane >> 2, hb);
+    return lds_u16(flag ? fa : va);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -277,9 +277,10 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
                 const HandState b = w.hand();
                 const uint32_t ka = hb_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, tbl);
                 const uint32_t kb = hb_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, tbl);
-                wa += ka > kb; wb += kb > ka; tie += ka == kb;
+                wa += (kb - ka) >> 31; wb += (ka - kb) >> 31;      // class codes are 16-bit: the sign bit of the difference
                 w.next(slive, 48);
             }
+            tie = (hi - lo) - wa - wb;
         }
         const uint32_t sa = warp_sum(wa), sb = warp_sum(wb), stie = warp_sum(tie);
         if ((threadIdx.x & 31) == 0) {
@@ -373,9 +374,10 @@ range_equity_kernel(const Matchup *__restrict__ mus, int n_mu, uint64_t board, u
                 const HandState b = w.hand();
                 const uint32_t ka = hb_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, tbl);
                 const uint32_t kb = hb_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, tbl);
-                ca += ka > kb; cb += kb > ka; ct += ka == kb;
+                ca += (kb - ka) >> 31; cb += (ka - kb) >> 31;      // class codes are 16-bit: the sign bit of the difference
                 w.next(slive, nl);
             }
+            ct = (hi - lo) - ca - cb;
         }
         const unsigned long long wgt = (unsigned long long)mu.weight;
         wa += wgt * ca; wb += wgt * cb; tie += wgt * ct; tot += wgt * (hi - lo);
@@ -646,10 +648,11 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         for (int q = 0; q < NR; q++) {
             const uint2 e1 = rep_of(card[q]), e2 = rep_of(card[q + NR]);
             const uint32_t t = b.t + e1.x + e2.x, sn = b.sn + e1.y + e2.y;
-            uint32_t k = hb_rank_class(t, tbl);
+            // (a divergent branch per seat measures faster here than the branch-free select of hb_class: 38.3 vs 37.5 G trials/s)
+            uint32_t k = lds_u16(hb_slot_addr(t, tbl));
             if (sn & 0x8888u) {
                 const uint32_t fm = lb | ((e1.y & cbit) ? (e1.y >> 16) : 0u) | ((e2.y & cbit) ? (e2.y >> 16) : 0u);
-                k = hb_flush_class(fm, tbl);
+                k = lds_u16(hb_flush_addr(fm, tbl));
             }
             key[q] = k;
         }
@@ -658,10 +661,10 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
             key[NR + s] = 0;
             if (s < nf) {
                 const uint32_t t = b.t + prm.h_t[s], sn = b.sn + prm.h_sn[s];
-                uint32_t k = hb_rank_class(t, tbl);
+                uint32_t k = lds_u16(hb_slot_addr(t, tbl));
                 if (sn & 0x8888u) {
                     const uint32_t hw = (cbit & 0x1100u) ? prm.h_mhi[s] : prm.h_mlo[s];
-                    k = hb_flush_class(lb | (((cbit & 0x1010u) ? (hw >> 16) : (hw & 0xFFFFu)) >> 2), tbl);
+                    k = lds_u16(hb_flush_addr(lb | (((cbit & 0x1010u) ? (hw >> 16) : (hw & 0xFFFFu)) >> 2), tbl));
                 }
                 key[NR + s] = k;
             }
