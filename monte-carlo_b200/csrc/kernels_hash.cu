@@ -25,7 +25,9 @@ __host__ __device__ __forceinline__ uint4 live_entry(const CardKey &k, int pos) 
 
 // Walks K-subsets of the live list in colex order, keeping the partial hands P[i] = base + cards c[i..K-1] in
 // registers: the common step (lowest card moves) costs one 16-byte shared load and four integer ops.
-template <int K>
+// LS = stride of the live list in entries: 1 for a plain list, 32 for a list replicated per lane ([entry][lane],
+// `live` then points at the lane's column), which makes the 16-byte loads of a warp conflict-free.
+template <int K, int LS = 1>
 struct Walker {
     int c[K > 0 ? K : 1];
     HandState P[K + 1];
@@ -35,7 +37,7 @@ struct Walker {
         if constexpr (K > 0) {
             colex_unrank<K>(idx, nl, sbin, c);
 #pragma unroll
-            for (int i = K - 1; i >= 0; i--) P[i] = with_card(P[i + 1], live[c[i]]);
+            for (int i = K - 1; i >= 0; i--) P[i] = with_card(P[i + 1], live[c[i] * LS]);
         }
     }
     template <int I>
@@ -47,7 +49,7 @@ struct Walker {
             } else {
                 if (c[I] >= nl) c[I] = nl;           // past the last subset: live[nl] is a zero entry
             }
-            P[I] = with_card(P[I + 1], live[c[I]]);
+            P[I] = with_card(P[I + 1], live[c[I] * LS]);
         }
     }
     __device__ __forceinline__ void next(const uint4 *live, int nl) { bump<0>(live, nl); }
@@ -237,8 +239,9 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
                     const CardKey *__restrict__ g_card, long long *__restrict__ wtl) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
-    uint4 *slive = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
-    uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX);
+    uint4 *slive = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));                  // [LIVE_MAX][32 lanes]
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX * 32);
+    __shared__ uint4 slist[LIVE_MAX];
     __shared__ unsigned long long sred[3];
     __shared__ CardKey scard[64];
     __shared__ unsigned long long mbar;
@@ -246,6 +249,7 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
     stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
     if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
+    const uint4 *my_live = slive + (threadIdx.x & 31);
     stage.wait();
     const uint32_t tbl = staged_table_base(H);
     const uint32_t total = cbinom(48, 5);
@@ -256,9 +260,11 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
         const uint64_t livem = DECK_MASK & ~(mu.hole_a | mu.hole_b);
         if (threadIdx.x < 64) {
             const int p = threadIdx.x;
-            if ((livem >> p) & 1ull) slive[__popcll(livem & ((1ull << p) - 1ull))] = live_entry(scard[p], p);
-            if (p >= 48 && p < LIVE_MAX) slive[p] = make_uint4(0, 0, 0, 0);
+            if ((livem >> p) & 1ull) slist[__popcll(livem & ((1ull << p) - 1ull))] = live_entry(scard[p], p);
+            if (p >= 48 && p < LIVE_MAX) slist[p] = make_uint4(0, 0, 0, 0);
         }
+        __syncthreads();
+        for (int i = threadIdx.x; i < LIVE_MAX * 32; i += PF_THREADS) slive[i] = slist[i >> 5];   // one copy per lane
         // the two hands' fixed parts
         HandState ha{0, 0, (uint32_t)mu.hole_a, (uint32_t)(mu.hole_a >> 32)}, hb{0, 0, (uint32_t)mu.hole_b, (uint32_t)(mu.hole_b >> 32)};
         {
@@ -271,14 +277,14 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
         const uint32_t lo = per * threadIdx.x, hi = min(total, lo + per);
         uint32_t wa = 0, wb = 0, tie = 0;
         if (lo < hi) {
-            Walker<5> w;
-            w.init(lo, 48, sbin, slive, HandState{0, SN_BIAS, 0, 0});
+            Walker<5, 32> w;
+            w.init(lo, 48, sbin, my_live, HandState{0, SN_BIAS, 0, 0});
             for (uint32_t i = lo; i < hi; i++) {
                 const HandState b = w.hand();
                 const uint32_t ka = hb_class(b.t + ha.t, b.sn + ha.sn, b.mlo | ha.mlo, b.mhi | ha.mhi, tbl);
                 const uint32_t kb = hb_class(b.t + hb.t, b.sn + hb.sn, b.mlo | hb.mlo, b.mhi | hb.mhi, tbl);
                 wa += (kb - ka) >> 31; wb += (ka - kb) >> 31;      // class codes are 16-bit: the sign bit of the difference
-                w.next(slive, 48);
+                w.next(my_live, 48);
             }
             tie = (hi - lo) - wa - wb;
         }
@@ -305,10 +311,11 @@ preflop_hash_kernel(const Matchup *__restrict__ mus, int n_mu, const HashBlob *_
 cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
                                 const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (n_matchups <= 0) return cudaSuccess;
-    cudaError_t e = cudaFuncSetAttribute(preflop_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
+    const size_t smem = sizeof(HashBlob) + LIVE_MAX * 32 * sizeof(uint4) + BIN_N * BIN_K * sizeof(uint32_t);
+    cudaError_t e = cudaFuncSetAttribute(preflop_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int grid = n_matchups < di.sm_count ? n_matchups : di.sm_count;
-    preflop_hash_kernel<<<grid, PF_THREADS, eqx_smem(), st>>>(d_matchups, n_matchups, tb.d_blob, tb.d_card, d_wtl);
+    preflop_hash_kernel<<<grid, PF_THREADS, smem, st>>>(d_matchups, n_matchups, tb.d_blob, tb.d_card, d_wtl);
     return cudaGetLastError();
 }
 
@@ -432,8 +439,8 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
                   unsigned long long *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
-    uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
-    uint4 *scat = sdeck + LIVE_MAX;                                   // 16 entries: {dense base, counter increments lo / hi, 0}
+    uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));                 // [LIVE_MAX][32 lanes]: one copy per lane
+    uint4 *scat = sdeck + LIVE_MAX * 32;                              // 16 entries: {dense base, counter increments lo / hi, 0}
     unsigned long long *sred = reinterpret_cast<unsigned long long *>(scat + 16);   // 16 words
     uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
     uint32_t *snib = sbin + BIN_N * BIN_K;
@@ -442,11 +449,12 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
     stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
     for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
-    if (threadIdx.x < LIVE_MAX) {
-        const int id = threadIdx.x;                                  // card id 13*suit + rank-2 -> bit position
+    for (int i = threadIdx.x; i < LIVE_MAX * 32; i += blockDim.x) {
+        const int id = i >> 5;                                       // card id 13*suit + rank-2 -> bit position
         const int p = id + 2 + 3 * (id / 13);
-        sdeck[id] = id < 52 ? live_entry(g_card[p], p) : make_uint4(0, 0, 0, 0);
+        sdeck[i] = id < 52 ? live_entry(g_card[p], p) : make_uint4(0, 0, 0, 0);
     }
+    const uint4 *my_deck = sdeck + (threadIdx.x & 31);
     if (threadIdx.x < 16) {
         const int c = threadIdx.x;                                   // categories 0..3: 8-bit fields of lo; 4..8: 6-bit fields of hi
         sred[c] = 0ull;
@@ -465,8 +473,8 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
     const uint64_t lo = me * per < count ? me * per : count;
     const uint64_t hi = lo + per < count ? lo + per : count;
     if (lo < hi) {
-        Walker<7> w;
-        w.init((uint32_t)(first + lo), 52, sbin, sdeck, HandState{0, SN_BIAS, 0, 0});
+        Walker<7, 32> w;
+        w.init((uint32_t)(first + lo), 52, sbin, my_deck, HandState{0, SN_BIAS, 0, 0});
         for (uint64_t base = lo; base < hi; base += ENUM_FOLD) {
             const uint32_t len = (uint32_t)(hi - base < (uint64_t)ENUM_FOLD ? hi - base : (uint64_t)ENUM_FOLD);
             uint32_t acc_lo = 0, acc_hi = 0, nsum = 0;                // nsum <= 32 * 2^24
@@ -476,7 +484,7 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
                 const uint4 ci = scat[code >> 12];
                 acc_lo += ci.y; acc_hi += ci.z;
                 nsum += snib[ci.x + (code & 0xFFFu)];
-                w.next(sdeck, 52);
+                w.next(my_deck, 52);
             }
 #pragma unroll
             for (int i = 0; i < 4; i++) h[i] += (acc_lo >> (8 * i)) & 255u;
@@ -498,7 +506,7 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
 }
 
 static size_t enum_smem(int n_classes) {
-    return sizeof(HashBlob) + (LIVE_MAX + 16) * sizeof(uint4) + 16 * sizeof(unsigned long long) +
+    return sizeof(HashBlob) + (LIVE_MAX * 32 + 16) * sizeof(uint4) + 16 * sizeof(unsigned long long) +
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
 }
 
