@@ -30,8 +30,8 @@ E2E_LOG2 = 26                    # hands per GPU per step through the host-buffe
 ALGO_BYTES_PER_EVAL = 12         # 8 B mask in + 4 B key out
 # thread-level instructions per unit.  SURVEY 8d declared 64 / 70 / 140 / 1024 and allows lowering them "with a SASS
 # count to justify it": these are the executed warp-instructions per unit that ncu measured for the current kernels
-# (profiles/r01_v_k1_v5_ncu_full.txt, profiles/r01_o_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
-OPS = {"eval": 46, "enum": 69, "board2": 78, "mc9": 702}
+# (profiles/r01_v_k1_v5_ncu_full.txt, profiles/r01_z_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
+OPS = {"eval": 46, "enum": 62, "board2": 69, "mc9": 685}
 METRIC = "7-card evals/s"
 
 
