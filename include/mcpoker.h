@@ -138,6 +138,17 @@ int  mc_preflop_matrix(int64_t *wtl /* 169*169*3 */);
 /* share `part` of `n_parts` of the suit-canonical matchup list (one process per GPU: part = rank); the full matrix
  * is the element-wise sum of the parts (one all-reduce of 169*169*3 int64) */
 int  mc_preflop_matrix_part(int part, int n_parts, int64_t *wtl /* 169*169*3 */, int32_t *n_matchups /* nullable */);
+/* The same matrix by BOARDS: every suit-canonical 5-card board (134,459, weight = orbit size) evaluates
+ * its 1,081 hole pairs once, sorts them and counts wins by class with a running scan, then removes the pairs of holes
+ * that share a card.  mc_preflop_wins_by_boards returns share `part` of `n_parts` of win[a][b] (169*169 int64; the
+ * full win matrix is the element-wise sum of the parts); mc_preflop_matrix_from_wins derives {win,tie,loss} from the
+ * full win matrix (host arithmetic: loss = win transposed, tie = pairs * C(48,5) - win - loss);
+ * mc_preflop_matrix_by_boards does both on the devices of this library instance.  Equal to mc_preflop_matrix cell
+ * by cell. */
+int  mc_preflop_boards_count(int32_t *n_boards /* nullable */, int64_t *weight_sum /* nullable */);
+int  mc_preflop_wins_by_boards(int part, int n_parts, int64_t *win /* 169*169 */, int32_t *n_boards /* nullable */);
+int  mc_preflop_matrix_from_wins(const int64_t *win /* 169*169 */, int64_t *wtl /* 169*169*3 */);
+int  mc_preflop_matrix_by_boards(int64_t *wtl /* 169*169*3 */);
 int  mc_preflop_cells(const int32_t *class_a, const int32_t *class_b, int n_cells, int64_t *wtl /* n*3 */);
 
 #ifdef __cplusplus

@@ -165,6 +165,38 @@ def preflop_matrix_part(part, n_parts):
     return out, n.value
 
 
+def preflop_boards_count():
+    """-> (number of suit-canonical 5-card boards, sum of their orbit sizes); host only, needs no GPU"""
+    n, w = C.c_int32(0), C.c_int64(0)
+    E.check(E.lib().mc_preflop_boards_count(C.byref(n), C.byref(w)))
+    return n.value, w.value
+
+
+def preflop_wins_by_boards(part=0, n_parts=1):
+    """-> (this part's share of the 169x169 win matrix computed board by board, number of canonical boards it covered)"""
+    E.ensure_init()
+    out = np.zeros((E.N_CLASSES, E.N_CLASSES), dtype=np.int64)
+    n = C.c_int32(0)
+    E.check(E.lib().mc_preflop_wins_by_boards(part, n_parts, out.ctypes.data, C.byref(n)))
+    return out, n.value
+
+
+def preflop_matrix_from_wins(win):
+    """full win matrix -> 169x169x3 {win, tie, loss} (host arithmetic)"""
+    win = np.ascontiguousarray(win, dtype=np.int64)
+    out = np.zeros((E.N_CLASSES, E.N_CLASSES, 3), dtype=np.int64)
+    E.check(E.lib().mc_preflop_matrix_from_wins(win.ctypes.data, out.ctypes.data))
+    return out
+
+
+def preflop_matrix_by_boards():
+    """the 169x169x3 matrix by the per-board sort-and-count formulation; equal to preflop_matrix() cell by cell"""
+    E.ensure_init()
+    out = np.zeros((E.N_CLASSES, E.N_CLASSES, 3), dtype=np.int64)
+    E.check(E.lib().mc_preflop_matrix_by_boards(out.ctypes.data))
+    return out
+
+
 def hole_class(rank_a, rank_b, suited):
     """169-class id: x = rank-2; pair 13x+x; suited 13*hi+lo; offsuit 13*lo+hi"""
     hi, lo = max(rank_a, rank_b) - 2, min(rank_a, rank_b) - 2

@@ -16,6 +16,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace mcp;
@@ -48,6 +49,9 @@ struct DevCtx {
     uint32_t ticket = 0;                          // sequence number of the single-call kernels (await_ticket)
     Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
     long long *d_wtl = nullptr;
+    PfBoard *d_pb_boards = nullptr; size_t pb_board_cap = 0;            // config 5 by boards: board list, scratch, win matrix
+    uint32_t *d_pb_scratch = nullptr;
+    unsigned long long *d_pb_win = nullptr;
     DeviceTables tb;                              // perfect-hash evaluator tables (hashtab.cuh), built at init
     void *d_tables = nullptr;                     // one allocation: blob | card keys | nibble keys
 
@@ -63,6 +67,9 @@ struct DevCtx {
         if (h_small) cudaFreeHost(h_small);
         if (d_matchups) cudaFree(d_matchups);
         if (d_wtl) cudaFree(d_wtl);
+        if (d_pb_boards) cudaFree(d_pb_boards);
+        if (d_pb_scratch) cudaFree(d_pb_scratch);
+        if (d_pb_win) cudaFree(d_pb_win);
         if (d_tables) cudaFree(d_tables);
         if (stream) cudaStreamDestroy(stream);
     }
@@ -756,6 +763,138 @@ int mc_preflop_matrix_part(int part, int n_parts, int64_t *wtl, int32_t *n_match
     if (n_matchups) *n_matchups = (int32_t)mine.size();
     return MC_OK;
 }
+// ---- config 5 by boards (K7) -----------------------------------------------------------
+namespace {
+constexpr int PB_CHUNK = 16384;                       // boards per launch pair: 2 x 16384 x 1088 x 4 B = 143 MB of scratch
+// 5-card boards folded by the 24 suit permutations: one representative (the lexicographically smallest image as a
+// sorted list of card ids) per orbit, weight = orbit size.  134,459 boards, weights sum to C(52,5).
+const std::vector<PfBoard> &canonical_boards() {
+    static std::mutex mu;
+    static std::vector<PfBoard> all;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!all.empty()) return all;
+    int perms[24][4], np = 0;
+    int p[4] = {0, 1, 2, 3};
+    do { std::memcpy(perms[np++], p, sizeof p); } while (std::next_permutation(p, p + 4));
+    const int nt = (int)std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    std::vector<std::vector<PfBoard>> found(48);     // by first card id, so that the concatenation is ordered
+    auto work = [&](int t) {
+        for (int c0 = t; c0 < 48; c0 += nt)
+            for (int c1 = c0 + 1; c1 < 49; c1++) for (int c2 = c1 + 1; c2 < 50; c2++)
+                for (int c3 = c2 + 1; c3 < 51; c3++) for (int c4 = c3 + 1; c4 < 52; c4++) {
+                    const int c[5] = {c0, c1, c2, c3, c4};
+                    int stab = 0;
+                    bool canonical = true;
+                    for (int q = 0; q < 24 && canonical; q++) {
+                        int img[5];
+                        for (int k = 0; k < 5; k++) img[k] = 13 * perms[q][c[k] / 13] + c[k] % 13;
+                        std::sort(img, img + 5);
+                        int cmp = 0;
+                        for (int k = 0; k < 5 && !cmp; k++) cmp = img[k] - c[k];
+                        if (cmp < 0) canonical = false;
+                        stab += cmp == 0;
+                    }
+                    if (!canonical) continue;
+                    PfBoard b{};
+                    for (int k = 0; k < 5; k++) b.card[k] = (unsigned char)(16 * (c[k] / 13) + c[k] % 13 + 2);
+                    b.weight = (unsigned char)(24 / stab);
+                    found[c0].push_back(b);
+                }
+    };
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; t++) th.emplace_back(work, t);
+    for (auto &t : th) t.join();
+    for (auto &v : found) all.insert(all.end(), v.begin(), v.end());
+    return all;
+}
+}  // namespace
+
+int mc_preflop_boards_count(int32_t *n_boards, int64_t *weight_sum) {
+    const std::vector<PfBoard> &all = canonical_boards();
+    if (n_boards) *n_boards = (int32_t)all.size();
+    if (weight_sum) { int64_t s = 0; for (auto &b : all) s += b.weight; *weight_sum = s; }
+    return MC_OK;
+}
+
+int mc_preflop_wins_by_boards(int part, int n_parts, int64_t *win, int32_t *n_boards) {
+    if (!win || n_parts < 1 || part < 0 || part >= n_parts) return fail(MC_ERR_INVALID, "bad part / n_parts");
+    int rc = need_init();
+    if (rc) return rc;
+    const std::vector<PfBoard> &all = canonical_boards();
+    std::vector<PfBoard> mine;
+    for (size_t i = (size_t)part; i < all.size(); i += (size_t)n_parts) mine.push_back(all[i]);
+    if (n_boards) *n_boards = (int32_t)mine.size();
+    const int nd = (int)g_ctx.size();
+    const size_t cells = (size_t)MC_N_CLASSES * MC_N_CLASSES;
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    std::vector<std::vector<PfBoard>> share(nd);
+    for (size_t i = 0; i < mine.size(); i++) share[i % nd].push_back(mine[i]);
+    std::vector<std::vector<unsigned long long>> host(nd, std::vector<unsigned long long>(cells));
+    for (int d = 0; d < nd; d++) {
+        DevCtx &c = *g_ctx[d];
+        CU(cudaSetDevice(c.device));
+        if (!c.d_pb_win) CU(cudaMalloc(&c.d_pb_win, cells * sizeof(unsigned long long)));
+        if (!c.d_pb_scratch) CU(cudaMalloc(&c.d_pb_scratch, (size_t)2 * PB_CHUNK * PB_STRIDE * sizeof(uint32_t)));
+        if (c.pb_board_cap < share[d].size()) {
+            if (c.d_pb_boards) cudaFree(c.d_pb_boards);
+            CU(cudaMalloc(&c.d_pb_boards, share[d].size() * sizeof(PfBoard)));
+            c.pb_board_cap = share[d].size();
+        }
+        CU(cudaMemsetAsync(c.d_pb_win, 0, cells * sizeof(unsigned long long), c.stream));
+        if (!share[d].empty())
+            CU(cudaMemcpyAsync(c.d_pb_boards, share[d].data(), share[d].size() * sizeof(PfBoard), cudaMemcpyHostToDevice, c.stream));
+        for (size_t off = 0; off < share[d].size(); off += PB_CHUNK) {
+            const int n = (int)std::min<size_t>(PB_CHUNK, share[d].size() - off);
+            CU(launch_preflop_boards(c.d_pb_boards + off, n, c.d_pb_scratch, c.d_pb_scratch + (size_t)PB_CHUNK * PB_STRIDE,
+                                     c.d_pb_win, c.tb, c.info, c.stream));
+        }
+        CU(cudaMemcpyAsync(host[d].data(), c.d_pb_win, cells * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    }
+    for (size_t i = 0; i < cells; i++) win[i] = 0;
+    for (int d = 0; d < nd; d++) {
+        CU(cudaSetDevice(g_ctx[d]->device));
+        CU(cudaStreamSynchronize(g_ctx[d]->stream));
+        for (size_t i = 0; i < cells; i++) win[i] += (int64_t)host[d][i];
+    }
+    return MC_OK;
+}
+
+int mc_preflop_matrix_from_wins(const int64_t *win, int64_t *wtl) {
+    if (!win || !wtl) return fail(MC_ERR_INVALID, "null argument");
+    // ordered pairs of disjoint holes per cell; each meets on C(48,5) boards
+    static std::vector<int64_t> pairs;
+    static std::mutex mu;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (pairs.empty()) {
+            pairs.assign((size_t)MC_N_CLASSES * MC_N_CLASSES, 0);
+            std::vector<uint64_t> holes;
+            for (int a = 0; a < 52; a++) for (int b = a + 1; b < 52; b++) holes.push_back(mc_card_bit(a) | mc_card_bit(b));
+            std::vector<int> cls(holes.size());
+            for (size_t i = 0; i < holes.size(); i++) cls[i] = hole_class(holes[i]);
+            for (size_t i = 0; i < holes.size(); i++) for (size_t j = 0; j < holes.size(); j++)
+                if (!(holes[i] & holes[j])) pairs[(size_t)cls[i] * MC_N_CLASSES + cls[j]]++;
+        }
+    }
+    const int64_t boards = (int64_t)host_binom(48, 5);
+    for (int a = 0; a < MC_N_CLASSES; a++) for (int b = 0; b < MC_N_CLASSES; b++) {
+        const size_t ab = (size_t)a * MC_N_CLASSES + b, ba = (size_t)b * MC_N_CLASSES + a;
+        wtl[3 * ab + 0] = win[ab];
+        wtl[3 * ab + 1] = pairs[ab] * boards - win[ab] - win[ba];
+        wtl[3 * ab + 2] = win[ba];
+    }
+    return MC_OK;
+}
+
+int mc_preflop_matrix_by_boards(int64_t *wtl) {
+    if (!wtl) return fail(MC_ERR_INVALID, "wtl is null");
+    std::vector<int64_t> win((size_t)MC_N_CLASSES * MC_N_CLASSES);
+    int rc = mc_preflop_wins_by_boards(0, 1, win.data(), nullptr);
+    if (rc) return rc;
+    return mc_preflop_matrix_from_wins(win.data(), wtl);
+}
+
 int mc_preflop_cells(const int32_t *class_a, const int32_t *class_b, int n_cells, int64_t *wtl) {
     if (!class_a || !class_b || !wtl || n_cells <= 0) return fail(MC_ERR_INVALID, "bad cell list");
     std::vector<std::pair<int, int>> cells;

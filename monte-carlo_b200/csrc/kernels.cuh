@@ -69,6 +69,13 @@ cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long 
 cudaError_t launch_range_equity(const Matchup *d_matchups, int n_matchups, uint64_t board, uint64_t dead, long long *d_out,
                                 const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
 
+// config 5 by boards (kernels_boards.cu): d_win = 169 x 169 u64, win[a][b] += weight * #{hole of class a
+// beats a disjoint hole of class b on the board}; d_sorted / d_info: PB_STRIDE words of scratch per board
+struct PfBoard { unsigned char card[5]; unsigned char weight; unsigned char pad[2]; };   // bit positions, orbit size
+constexpr int PB_STRIDE = 1088;
+cudaError_t launch_preflop_boards(const PfBoard *d_boards, int n_boards, uint32_t *d_sorted, uint32_t *d_info,
+                                  unsigned long long *d_win, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+
 uint64_t host_binom(int n, int k);
 
 }  // namespace mcp

@@ -23,6 +23,7 @@ EXPORTS = [
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
     "mc_equity_mc", "mc_equity_mc_dev", "mc_equity_ranges", "mc_preflop_matrix", "mc_preflop_matrix_part", "mc_preflop_cells",
+    "mc_preflop_boards_count", "mc_preflop_wins_by_boards", "mc_preflop_matrix_from_wins", "mc_preflop_matrix_by_boards",
 ]
 
 
@@ -86,6 +87,10 @@ def lib():
     L.mc_preflop_matrix.argtypes = [vp]
     L.mc_preflop_matrix_part.argtypes = [C.c_int, C.c_int, vp, P(i32)]
     L.mc_preflop_cells.argtypes = [P(i32), P(i32), C.c_int, vp]
+    L.mc_preflop_boards_count.argtypes = [P(i32), P(i64)]
+    L.mc_preflop_wins_by_boards.argtypes = [C.c_int, C.c_int, vp, P(i32)]
+    L.mc_preflop_matrix_from_wins.argtypes = [vp, vp]
+    L.mc_preflop_matrix_by_boards.argtypes = [vp]
     _lib = L
     return L
 

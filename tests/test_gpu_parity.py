@@ -332,6 +332,19 @@ def test_preflop_matrix_full_properties(gpu):
     assert np.array_equal(p0 + p1 + p2, m) and n0 + n1 + n2 > 40000
 
 
+def test_preflop_matrix_by_boards_equals_brute_force(gpu):
+    """the per-board sort-and-count formulation (134,459 suit-canonical boards, 1,081 holes evaluated
+    once per board) must reproduce the brute-force matrix of K5 cell by cell, also when dealt out in parts."""
+    api = gpu.api
+    want = api.preflop_matrix()
+    got = api.preflop_matrix_by_boards()
+    assert np.array_equal(got, want)
+    w0, n0 = api.preflop_wins_by_boards(0, 2)
+    w1, n1 = api.preflop_wins_by_boards(1, 2)
+    assert n0 + n1 == 134459
+    assert np.array_equal(api.preflop_matrix_from_wins(w0 + w1), want)
+
+
 def test_abi_is_thread_safe(gpu, oracle):
     """the reference calls the evaluator from one go-block per room (board.clj:122-129): many host threads at once"""
     import threading

@@ -152,3 +152,10 @@ def test_settle_pots_matches_oracle_and_mirror(pkg, oracle):
     # a pot whose players all folded: the reference divides by zero; the ABI reports MC_ERR_INVALID
     with pytest.raises(pkg.engine.McError):
         pkg.api.settle_pots([0, -1], [(10, 2, [1])])
+
+
+def test_canonical_boards_cover_every_board(pkg):
+    """the suit-canonical 5-card boards of the per-board matrix: 134,459 orbits whose sizes sum to
+    C(52,5); host-only enumeration, no GPU"""
+    n, w = pkg.api.preflop_boards_count()
+    assert n == 134459 and w == 2598960
