@@ -12,6 +12,7 @@
 #include "kernels.cuh"
 #include "common.cuh"
 #include "hashtab.cuh"
+#include <algorithm>
 
 namespace mcp {
 
@@ -126,7 +127,8 @@ pf_board_eval_kernel(const PfBoard *__restrict__ boards, int nb, const HashBlob 
             const int h = threadIdx.x + r * PB_THREADS;
             if (h < PB_HOLES) {
                 const uint32_t pos = atomicAdd(&shist[dense[r]], 1u);
-                out_sorted[(size_t)bi * PB_STRIDE + pos] = info[r];
+                // sorted word: strength << 16 | byte offset of the hole class's row of 16-bit counters (K7b adds there)
+                out_sorted[(size_t)bi * PB_STRIDE + pos] = dense[r] << 16 | ((info[r] & 255u) * (PB_WORDS * 4u));
                 out_info[(size_t)bi * PB_STRIDE + h] = info[r];
             }
         }
@@ -136,25 +138,86 @@ pf_board_eval_kernel(const PfBoard *__restrict__ boards, int nb, const HashBlob 
 
 // ---------------------------------------------------------------------------------------------------
 // K7b: the win matrix.  A block keeps 169 x 169 32-bit counters and a 16-bit copy (two classes per word) that the
-// boards add into and that is folded into the 32-bit counters every PB_FLUSH boards.  All updates are word-wide
-// atomics, so the scan and the corrections of a board run concurrently in any order: a 16-bit field may go
-// "negative" in between, the word arithmetic stays exact and every field is back in range when its boards are done.
+// boards add into and that is folded into the 32-bit counters every PB_FLUSH boards.  Four boards are in flight per
+// block, eight warps each: three warps scan the sorted holes (a scan step is a short dependent chain, so one board
+// alone leaves the SM idle), five warps walk the pairs of holes with a common card.  All updates are word-wide shared
+// atomics, so scans and corrections of different boards run concurrently in any order: a 16-bit field may go
+// "negative" in between, the word arithmetic stays exact and every field is back in range at the fold.
 // ---------------------------------------------------------------------------------------------------
+constexpr int PB_GROUPS = 4, PB_GROUP_THREADS = PB_THREADS / PB_GROUPS;   // boards in flight per block, threads per board
+constexpr int PB_CORR_WARPS = PB_GROUP_THREADS / 32 - PB_SCAN_THREADS / 32;
+static_assert(PB_FLUSH % PB_GROUPS == 0, "a fold follows a whole number of rounds");
+static_assert(PB_WORDS * 4 * (PB_CLASSES - 1) < 65536, "row offsets fit the low half of a sorted word");
+
+__device__ __forceinline__ void pb_group_sync(int group) {
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + group), "r"(PB_GROUP_THREADS) : "memory");
+}
+
 __global__ void __launch_bounds__(PB_THREADS, 1)
 pf_board_count_kernel(const PfBoard *__restrict__ boards, int nb, const uint32_t *__restrict__ g_sorted,
                       const uint32_t *__restrict__ g_info, unsigned long long *__restrict__ g_win) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t *W32 = reinterpret_cast<uint32_t *>(smem_raw);                 // [169][169]
     uint32_t *W16 = W32 + PB_CLASSES * PB_CLASSES;                          // [169][PB_WORDS]
-    uint32_t *sp = W16 + PB_CLASSES * PB_WORDS;                             // sorted words of the current board
-    uint32_t *ip = sp + PB_STRIDE;                                          // info words by hole index
+    uint32_t *sbuf = W16 + PB_CLASSES * PB_WORDS;                           // per group: sorted words, info words
+    uint32_t *srow = sbuf + PB_GROUPS * 2 * PB_STRIDE;                      // per correction warp: the 46 holes of one card
     __shared__ uint16_t spair[PB_HOLES + 1];
     pb_fill_pairs(spair);
     for (int i = threadIdx.x; i < PB_CLASSES * PB_CLASSES; i += PB_THREADS) W32[i] = 0u;
     for (int i = threadIdx.x; i < PB_CLASSES * PB_WORDS; i += PB_THREADS) W16[i] = 0u;
     __syncthreads();
 
-    auto fold = [&]() {
+    const int group = threadIdx.x / PB_GROUP_THREADS, gt = threadIdx.x % PB_GROUP_THREADS, lane = threadIdx.x & 31;
+    uint32_t *sp = sbuf + group * 2 * PB_STRIDE, *ip = sp + PB_STRIDE;
+    const uint32_t w16 = (uint32_t)__cvta_generic_to_shared(W16);
+    // a block takes contiguous batches of PB_FLUSH boards; group g plays boards g, g + 4, ... of the batch
+    for (int batch = blockIdx.x * PB_FLUSH; batch < nb; batch += gridDim.x * PB_FLUSH) {
+        for (int bi = batch + group; bi < min(nb, batch + PB_FLUSH); bi += PB_GROUPS) {
+            const uint32_t wgt = boards[bi].weight;
+            for (int i = gt; i < PB_HOLES; i += PB_GROUP_THREADS) {
+                sp[i] = g_sorted[(size_t)bi * PB_STRIDE + i];
+                ip[i] = g_info[(size_t)bi * PB_STRIDE + i];
+            }
+            pb_group_sync(group);
+            if (gt < PB_SCAN_THREADS) {
+                // ascending strength: `running` = holes strictly weaker than the current one, by class (this lane's two classes)
+                if (gt < PB_WORDS) {
+                    const uint32_t my = w16 + 4u * gt, own0 = 2u * gt * (PB_WORDS * 4u), own1 = own0 + PB_WORDS * 4u;
+                    uint32_t running = 0, pending = 0, prev = 0xFFFFFFFFu;
+#pragma unroll 4
+                    for (int i = 0; i < PB_HOLES; i++) {
+                        const uint32_t e = sp[i], d = e >> 16, ro = e & 0xFFFFu;
+                        if (d != prev) { running += pending; pending = 0u; prev = d; }
+                        asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(my + ro), "r"(running) : "memory");
+                        pending += ro == own0 ? wgt : (ro == own1 ? wgt << 16 : 0u);
+                    }
+                }
+            } else {
+                // pairs of holes with a common card were counted above as if they could meet: take them out again.
+                // A warp takes one common card at a time: its 46 holes go to a row, then the C(46,2) pairs are compared.
+                const int cw = (gt - PB_SCAN_THREADS) >> 5;
+                uint32_t *row = srow + (group * PB_CORR_WARPS + cw) * 48;
+                for (int c = cw; c < PB_LIVE; c += PB_CORR_WARPS) {
+                    for (int u = lane; u < PB_LIVE - 1; u += 32) {
+                        const int li = u + (u >= c);
+                        row[u] = ip[li < c ? c * (c - 1) / 2 + li : li * (li - 1) / 2 + c];
+                    }
+                    __syncwarp();
+                    for (int p = lane; p < (PB_LIVE - 1) * (PB_LIVE - 2) / 2; p += 32) {
+                        const uint32_t pr = spair[p];
+                        const uint32_t x = row[pr & 255u], y = row[pr >> 8];
+                        if ((x >> 8) != (y >> 8)) {
+                            const bool xw = (x >> 8) > (y >> 8);
+                            const uint32_t a = (xw ? x : y) & 255u, b = (xw ? y : x) & 255u;
+                            atomicSub(&W16[a * PB_WORDS + (b >> 1)], wgt << (16u * (b & 1u)));
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+            pb_group_sync(group);
+        }
+        __syncthreads();
         for (int i = threadIdx.x; i < PB_CLASSES * PB_WORDS; i += PB_THREADS) {
             const uint32_t w = W16[i];
             if (w) {
@@ -164,52 +227,8 @@ pf_board_count_kernel(const PfBoard *__restrict__ boards, int nb, const uint32_t
                 if (2 * l + 1 < PB_CLASSES) W32[a * PB_CLASSES + 2 * l + 1] += w >> 16;
             }
         }
-    };
-
-    int since_fold = 0;
-    for (int bi = blockIdx.x; bi < nb; bi += gridDim.x) {
-        const uint32_t wgt = boards[bi].weight;
-        for (int i = threadIdx.x; i < PB_HOLES; i += PB_THREADS) {
-            sp[i] = g_sorted[(size_t)bi * PB_STRIDE + i];
-            ip[i] = g_info[(size_t)bi * PB_STRIDE + i];
-        }
         __syncthreads();
-        if (threadIdx.x < PB_SCAN_THREADS) {
-            // ascending strength: `running` = holes strictly weaker than the current one, by class (this lane's two classes)
-            const uint32_t L = threadIdx.x;
-            if (L < (uint32_t)PB_WORDS) {
-                uint32_t running = 0, pending = 0, prev = 0xFFFFFFFFu;
-#pragma unroll 4
-                for (int i = 0; i < PB_HOLES; i++) {
-                    const uint32_t e = sp[i], d = e >> 8, a = e & 255u;
-                    if (d != prev) { running += pending; pending = 0u; prev = d; }
-                    if (running) atomicAdd(&W16[a * PB_WORDS + L], running);
-                    if ((a >> 1) == L) pending += wgt << (16u * (a & 1u));
-                }
-            }
-        } else {
-            // pairs of holes with a common card were counted above as if they could meet: take them out again
-            const int n_items = PB_LIVE * ((PB_LIVE - 1) * (PB_LIVE - 2) / 2);
-            for (int k = threadIdx.x - PB_SCAN_THREADS; k < n_items; k += PB_THREADS - PB_SCAN_THREADS) {
-                const int c = k / 1035, p = k - c * 1035;                   // common card, pair (u < v) of the other 46
-                const uint32_t pr = spair[p];
-                int u = pr & 255u, v = pr >> 8;
-                u += (u >= c); v += (v >= c);
-                const int ha = u < c ? c * (c - 1) / 2 + u : u * (u - 1) / 2 + c;
-                const int hb = v < c ? c * (c - 1) / 2 + v : v * (v - 1) / 2 + c;
-                const uint32_t x = ip[ha], y = ip[hb];
-                if ((x >> 8) != (y >> 8)) {
-                    const uint32_t win = (x >> 8) > (y >> 8) ? x : y, los = (x >> 8) > (y >> 8) ? y : x;
-                    const uint32_t a = win & 255u, b = los & 255u;
-                    atomicSub(&W16[a * PB_WORDS + (b >> 1)], wgt << (16u * (b & 1u)));
-                }
-            }
-        }
-        __syncthreads();
-        if (++since_fold == PB_FLUSH) { fold(); since_fold = 0; __syncthreads(); }
     }
-    fold();
-    __syncthreads();
     for (int i = threadIdx.x; i < PB_CLASSES * PB_CLASSES; i += PB_THREADS)
         if (W32[i]) atomicAdd(&g_win[i], (unsigned long long)W32[i]);
 }
@@ -218,7 +237,8 @@ cudaError_t launch_preflop_boards(const PfBoard *d_boards, int n_boards, uint32_
                                   unsigned long long *d_win, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (n_boards <= 0) return cudaSuccess;
     const size_t smem_a = sizeof(HashBlob) + PB_BINS * sizeof(uint32_t);
-    const size_t smem_b = ((size_t)PB_CLASSES * PB_CLASSES + (size_t)PB_CLASSES * PB_WORDS + 2 * PB_STRIDE) * sizeof(uint32_t);
+    const size_t smem_b = ((size_t)PB_CLASSES * PB_CLASSES + (size_t)PB_CLASSES * PB_WORDS + (size_t)PB_GROUPS * 2 * PB_STRIDE +
+                           (size_t)PB_GROUPS * PB_CORR_WARPS * 48) * sizeof(uint32_t);
     cudaError_t e = cudaFuncSetAttribute(pf_board_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(pf_board_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b);
@@ -227,7 +247,8 @@ cudaError_t launch_preflop_boards(const PfBoard *d_boards, int n_boards, uint32_
     pf_board_eval_kernel<<<grid, PB_THREADS, smem_a, st>>>(d_boards, n_boards, tb.d_blob, tb.d_card, tb.cat_base, d_sorted, d_info);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    pf_board_count_kernel<<<grid, PB_THREADS, smem_b, st>>>(d_boards, n_boards, d_sorted, d_info, d_win);
+    const int grid_b = std::min(di.sm_count, (n_boards + PB_FLUSH - 1) / PB_FLUSH);
+    pf_board_count_kernel<<<grid_b, PB_THREADS, smem_b, st>>>(d_boards, n_boards, d_sorted, d_info, d_win);
     return cudaGetLastError();
 }
 
