@@ -206,7 +206,7 @@ int current_tables(DeviceInfo *di, const DeviceTables **tb) {
     return fail(MC_ERR_NOT_INIT, "mc_init / mc_init_devices has not been called for the current device");
 }
 
-// K1 dispatch.  key_format: 0 nibble (auto: hash kernel for large aligned batches, else the rank-set-table kernel),
+// K1 dispatch.  key_format: 0 nibble (the plane-hash kernel for aligned buffers, else the rank-set-table kernel),
 // 1 packed, 2 nibble via FLO loops, 3 nibble via the rank-set table, 4 nibble via the hash tables (A/B variants)
 // the plane-hash kernel serves every aligned batch: measured (tools/k1_crossover.py) it wins at every size (6 us floor:
 // 184 KB staged by TMA; the rank-set-table kernel computes its 64 KB table in every block, 12 us)

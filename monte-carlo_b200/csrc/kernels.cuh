@@ -12,9 +12,9 @@ constexpr int MAX_SEATS = 9;
 // K1 variants (DESIGN.md "K1"): how the public nibble key is produced
 enum K1Mode : int {
     K1_PACKED = 0,        // packed key, no conversion
-    K1_NIBBLE_TABLE = 1,  // nibble key through the shared-memory rank-set table (default)
+    K1_NIBBLE_TABLE = 1,  // nibble key through the shared-memory rank-set table (v2; unaligned buffers and A/B)
     K1_NIBBLE_FLO = 2,    // nibble key through FLO/clz loops, no table (A/B variant)
-    K1_NIBBLE_HASH = 3,   // nibble key through the additive-key / perfect-hash tables (large aligned batches)
+    K1_NIBBLE_HASH = 3,   // nibble key through the plane-hash tables (eval7_stream_hash_kernel; default for aligned buffers)
 };
 
 struct DeviceInfo { int sm_count; int device; };
