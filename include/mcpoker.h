@@ -74,6 +74,11 @@ int  mc_key_decode(uint32_t nibble_key, int32_t *cat, int32_t hit[5], int32_t *n
 int  mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards /* 5..7 */, uint32_t *key);
 int  mc_eval7_batch(const uint64_t *masks, size_t n, uint32_t *keys);                 /* host buffers */
 int  mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_format);
+/* Page-locked host memory for the buffers of the host-buffer calls: they copy straight from / into the caller's
+ * memory, which runs at the full host-link rate only when it is pinned (a JVM caller wraps the pointer in a direct
+ * ByteBuffer).  Pageable buffers are accepted everywhere, just slower.  Needs mc_init. */
+void *mc_alloc_host(size_t bytes);                                                     /* NULL on failure (mc_last_error) */
+int  mc_free_host(void *p);
 int  mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void *stream);
 int  mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream);
 int  mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,

@@ -378,6 +378,21 @@ int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_
     }
     return MC_OK;
 }
+void *mc_alloc_host(size_t bytes) {
+    if (need_init()) return nullptr;
+    void *p = nullptr;
+    if (cudaSetDevice(g_ctx[0]->device) != cudaSuccess || cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+        fail(MC_ERR_CUDA, "cudaHostAlloc failed");
+        (void)cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+int mc_free_host(void *p) {
+    if (!p) return MC_OK;
+    CU(cudaFreeHost(p));
+    return MC_OK;
+}
 int mc_eval7_batch(const uint64_t *masks, size_t n, uint32_t *keys) {
     return mc_eval7_batch_fmt(masks, n, keys, MC_KEY_NIBBLE);
 }

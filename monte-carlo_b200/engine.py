@@ -24,6 +24,7 @@ EXPORTS = [
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
     "mc_equity_mc", "mc_equity_mc_dev", "mc_equity_ranges", "mc_preflop_matrix", "mc_preflop_matrix_part", "mc_preflop_cells",
     "mc_preflop_boards_count", "mc_preflop_wins_by_boards", "mc_preflop_matrix_from_wins", "mc_preflop_matrix_by_boards",
+    "mc_alloc_host", "mc_free_host",
 ]
 
 
@@ -91,6 +92,9 @@ def lib():
     L.mc_preflop_wins_by_boards.argtypes = [C.c_int, C.c_int, vp, P(i32)]
     L.mc_preflop_matrix_from_wins.argtypes = [vp, vp]
     L.mc_preflop_matrix_by_boards.argtypes = [vp]
+    L.mc_alloc_host.argtypes = [C.c_size_t]
+    L.mc_alloc_host.restype = C.c_void_p
+    L.mc_free_host.argtypes = [C.c_void_p]
     _lib = L
     return L
 

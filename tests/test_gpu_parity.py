@@ -137,6 +137,21 @@ def test_k1_on_structured_hand_families(gpu, oracle):
         assert np.array_equal(gpu.api.eval7_batch(masks, key_format=4), oracle.eval_batch(masks, 0))
 
 
+def test_eval7_batch_from_library_pinned_buffers(gpu, oracle):
+    """mc_alloc_host / mc_free_host: the host-buffer call on page-locked buffers handed out by the library"""
+    import ctypes as C
+    L = gpu.engine.lib()
+    n = 300001
+    masks = oracle.random_hands(SEED + 9, 0, n)
+    pm, pk = L.mc_alloc_host(8 * n), L.mc_alloc_host(4 * n)
+    assert pm and pk
+    C.memmove(pm, masks.ctypes.data, 8 * n)
+    gpu.engine.check(L.mc_eval7_batch(C.cast(pm, C.POINTER(C.c_uint64)), n, C.cast(pk, C.POINTER(C.c_uint32))))
+    got = np.ctypeslib.as_array(C.cast(pk, C.POINTER(C.c_uint32)), shape=(n,)).copy()
+    assert np.array_equal(got, oracle.eval_batch(masks, 0))
+    assert L.mc_free_host(pm) == 0 and L.mc_free_host(pk) == 0 and L.mc_free_host(None) == 0
+
+
 def test_k1_every_seven_card_hand_key_by_key(gpu, oracle):
     """BASELINE target: 100 % bit-exact rank agreement on all 133,784,560 seven-card hands, key by key, through the
     host-buffer ABI call (the K1 hash kernel for these batch sizes) against the oracle's direct evaluator"""
