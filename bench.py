@@ -272,6 +272,13 @@ def run_ours(args):
     e2e_value = world * ne * e2e_steps / (e2e_ms * 1e-3)
     if rank == 0 and not torch.equal(h_keys[:check_n], keys[:check_n].cpu()):
         raise SystemExit("e2e keys differ from the device-resident run")
+    # the same call on pageable buffers (what a caller gets without mc_alloc_host / pinning)
+    pg_masks, pg_keys = h_masks.numpy().copy(), np.empty(ne, dtype=np.uint32)
+    E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
+    t0 = time.perf_counter()
+    E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
+    pageable_value = ne / (time.perf_counter() - t0)
+    del pg_masks, pg_keys
     # the host link alone: the same pinned buffers copied with nothing else running (what bounds e2e)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     masks[:ne].copy_(h_masks, non_blocking=True)
@@ -283,6 +290,7 @@ def run_ours(args):
     d2h_alone = 4 * ne / (ev[2].elapsed_time(ev[3]) * 1e-3) / 1e9
     link = {"h2d_alone_gbs": h2d_alone, "d2h_alone_gbs": d2h_alone, "h2d_in_e2e_gbs": 8 * e2e_value / world / 1e9,
             "d2h_in_e2e_gbs": 4 * e2e_value / world / 1e9, "frac_of_h2d_alone": 8 * e2e_value / world / 1e9 / h2d_alone,
+            "pageable_buffers_evals_per_s_per_gpu": pageable_value,
             "note": "e2e moves 12 B per hand over the host link, both directions at once; it is bound by the H2D direction"}
     del masks, keys
 
