@@ -78,6 +78,7 @@ struct BulkStage {
 // schedule them freely; u16 entries arrive zero-extended in a full register (a C++ uint16_t load is kept as a
 // 16-bit value and merged / masked with extra PRMT and LOP3 around every select or compare).
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+__device__ __forceinline__ uint2 lds_u32x2(uint32_t addr) { uint2 v; asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr)); return v; }
 __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
 // shared address of a table, to be taken AFTER BulkStage::wait(): every lds_* through it depends on this volatile
 // asm, so none can move above the wait, and the compiler keeps the base in a register instead of rebuilding it

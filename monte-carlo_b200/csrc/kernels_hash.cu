@@ -528,15 +528,17 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
 // steps by a multiply chain (x = r * m: the high word is the draw, the low word is the next r), which equals
 // Lemire's exact bounded sampler on the product of the three ranges; a trial in which a word ends in the
 // sampler's rejection zone (p ~ 2e-4 per trial) is dealt again from the next Philox attempt.  The thread's deck is a byte array in a
-// bank-private shared-memory column (13 words, stride = blockDim = 512), so every deck access of a warp is
-// conflict-free whatever the indices, and the byte address of position j is (j * 513 & 0x1F803) | 4 * tid.
+// bank-private shared-memory column (13 words, stride S = 1024 threads for the 768-thread block), so every deck
+// access of a warp is conflict-free whatever the indices, and the byte offset of position j is
+// (j * (S + 1) & (15 * 4S | 3)) | 4 * tid.  768 threads x 80 registers per SM: the 52 KB of decks, the 8 KB card
+// table and the 164 KB hash blob fill the 227 KB of shared memory (measured 512 / 640 / 768 threads: 40.7 / 42.8 /
+// 43.9 G trials/s, tools/k4_ab.py).
 // Seats are processed in kernel order: random seats first (cards q and q + NR of the deal, the order of
 // deal-hand gameplay.clj:63-75), then the fixed seats; seat_of[] maps back to the caller's seat numbers.
 // A card's table entry is {premultiplied rank key, suit-counter increment | rank bit << 16}: the low half of the
 // second word counts suits, the high half rebuilds the flush lane without touching the card mask.
 // ---------------------------------------------------------------------------------------------------
-constexpr int MC_THREADS = 512;
-constexpr int MC_T4 = 4 * MC_THREADS;
+constexpr int MC_REP = 16;                    // lanes the card table is replicated over: an LDS.64 is served per half-warp
 constexpr uint32_t TAG_DEAL4 = 0x4D434434u;
 constexpr int MC_MAX_STEPS = 2 * MAX_SEATS + 5;
 
@@ -569,22 +571,24 @@ __device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t 
     o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
 }
 
-template <int NR>
+template <int NR, int MC_THREADS>
 __global__ void __launch_bounds__(MC_THREADS, 1)
 equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__restrict__ g_blob,
                     const CardKey *__restrict__ g_card, long long *__restrict__ d_counts) {
     using SH = McShape<NR>;
+    constexpr int MC_STRIDE = MC_THREADS <= 512 ? 512 : 1024;                                // deck column stride in words (power of two)
+    constexpr int MC_T4 = 4 * MC_STRIDE;
+    constexpr uint32_t J_MUL = MC_STRIDE + 1, J_MASK = (15u * MC_T4) | 3u;                   // j * J_MUL & J_MASK = (j >> 2) * MC_T4 + (j & 3)
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ __align__(16) unsigned char sdeck[13 * MC_T4];                                // [13 words][512 threads]; static: its
-                                                                                             // address is an immediate of every LDS / STS
-    unsigned char *srep_b = smem_raw;                                                        // [64 cards][32 lanes] x 8 B
+    unsigned char *sdeck = smem_raw;                                                         // [13 words][stride]
+    unsigned char *srep_b = smem_raw + 13 * MC_T4;                                           // [64 cards][16 lanes] x 8 B
     uint2 *srep = reinterpret_cast<uint2 *>(srep_b);
-    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw + 64 * 32 * sizeof(uint2));
+    HashBlob *H = reinterpret_cast<HashBlob *>(srep_b + 64 * MC_REP * sizeof(uint2));
     unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words + the mbarrier
     BulkStage stage;
     stage.start(sred + 19, H, g_blob, (uint32_t)sizeof(HashBlob));
-    for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) {
-        const int p = i >> 5, r = p & 15;
+    for (int i = threadIdx.x; i < 64 * MC_REP; i += blockDim.x) {
+        const int p = i / MC_REP, r = p & 15;
         const CardKey k = g_card[p];
         srep[i] = make_uint2(k.rk, k.sn | ((r >= 2 && r <= 14) ? 1u << (16 + r - 2) : 0u));
     }
@@ -594,9 +598,10 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 
     const uint32_t tid4 = 4u * threadIdx.x;
     unsigned char *dk = sdeck + tid4;
-    const uint32_t lane8 = 8u * (threadIdx.x & 31);
-    // table entry of card a for this lane: byte address a * 256 + lane * 8, built by one PRMT
-    auto rep_of = [&](uint32_t a) -> uint2 { return *reinterpret_cast<const uint2 *>(srep_b + __byte_perm(a, lane8, 0x5504)); };
+    // table entry of card a for this lane: shared address a * 128 + (srep + (lane & 15) * 8), one IMAD (the FMA pipe is the
+    // idle one); the addend goes through staged_table_base so that the compiler keeps it whole in a register
+    const uint32_t rep_lane = staged_table_base(srep_b + 8u * (threadIdx.x & (MC_REP - 1)));
+    auto rep_of = [&](uint32_t a) -> uint2 { return lds_u32x2(a * (8u * MC_REP) + rep_lane); };
     const int nb = prm.n_board, nf = prm.n_fixed;
     uint32_t dinit[13];
 #pragma unroll
@@ -625,8 +630,8 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
                 if (i < 2 * NR || i - 2 * NR < nb) {                     // (else: community card already on the table)
                     const uint64_t x = (uint64_t)r * prm.m[i];           // hi = offset in [0, m), lo = the next r
                     r = (uint32_t)x;
-                    const uint32_t j513 = (uint32_t)(x >> 32) * 513u + (uint32_t)i * 513u;
-                    unsigned char *pj = sdeck + ((j513 & 0x1F803u) | tid4);   // word (j >> 2) of the column, byte j & 3
+                    const uint32_t jm = (uint32_t)(x >> 32) * J_MUL + (uint32_t)i * J_MUL;
+                    unsigned char *pj = sdeck + ((jm & J_MASK) | tid4);       // word (j >> 2) of the column, byte j & 3
                     const uint32_t a = *pj;
                     *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
                     card[i] = a;
@@ -677,16 +682,21 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
                 key[NR + s] = k;
             }
         }
-        // showdown (gameplay.clj:127-132): sole maximum wins, shared maximum ties
+        // showdown (gameplay.clj:127-132): sole maximum wins, shared maximum ties.  Class codes are 16-bit, so
+        // key + (0x10000 - best) carries into bit 16 exactly for the seats at the maximum: no compares, no predicates
         uint32_t best = 0;
 #pragma unroll
         for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) best = max(best, key[s]);
-        int nbest = 0;
+        const uint32_t cb = 0x10000u - best;
+        uint32_t at[MAX_SEATS], nbest = 0;
 #pragma unroll
-        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) nbest += (key[s] == best);
+        for (int s = 0; s < MAX_SEATS; s++) {
+            at[s] = 0;
+            if (s < NR || s - NR < nf) { at[s] = (key[s] + cb) >> 16; nbest += at[s]; }
+        }
         const uint32_t inc = nbest == 1 ? 0x10001u : 1u;
 #pragma unroll
-        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) { if (key[s] == best) acc[s] += inc; }
+        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) acc[s] += at[s] * inc;
         units++;
     }
 
@@ -710,14 +720,18 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     }
 }
 
-static size_t mc_smem() { return 64 * 32 * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
+static size_t mc_smem(int threads) { return 13 * 4 * (size_t)(threads <= 512 ? 512 : 1024) + 64 * MC_REP * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
+static int mc_threads() {
+    static const int t = [] { const char *e = getenv("MCP_K4_THREADS"); const int v = e ? atoi(e) : 0; return v == 512 || v == 640 ? v : 768; }();   // A/B knob of tools/k4_ab.py
+    return t;
+}
 
-template <int NR>
+template <int NR, int MC_THREADS>
 static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
-    auto kern = equity_mc_fy_kernel<NR>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mc_smem());
+    auto kern = equity_mc_fy_kernel<NR, MC_THREADS>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mc_smem(MC_THREADS));
     if (e != cudaSuccess) return e;
-    kern<<<grid, MC_THREADS, mc_smem(), st>>>(prm, tb.d_blob, tb.d_card, d_counts);
+    kern<<<grid, MC_THREADS, mc_smem(MC_THREADS), st>>>(prm, tb.d_blob, tb.d_card, d_counts);
     return cudaGetLastError();
 }
 
@@ -750,22 +764,23 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
         prm.thr[w] = (uint32_t)((1ull << 32) % prod);
     }
     const int grid = di.sm_count;
+    const int MC_THREADS = mc_threads();
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
     for (uint64_t done = 0; done < n_trials; done += per_launch) {
         prm.first = first_trial + done;
         prm.count = (n_trials - done) < per_launch ? (n_trials - done) : per_launch;
         cudaError_t e;
         switch (nr) {
-            case 0: e = launch_mc<0>(prm, tb, d_counts, grid, st); break;
-            case 1: e = launch_mc<1>(prm, tb, d_counts, grid, st); break;
-            case 2: e = launch_mc<2>(prm, tb, d_counts, grid, st); break;
-            case 3: e = launch_mc<3>(prm, tb, d_counts, grid, st); break;
-            case 4: e = launch_mc<4>(prm, tb, d_counts, grid, st); break;
-            case 5: e = launch_mc<5>(prm, tb, d_counts, grid, st); break;
-            case 6: e = launch_mc<6>(prm, tb, d_counts, grid, st); break;
-            case 7: e = launch_mc<7>(prm, tb, d_counts, grid, st); break;
-            case 8: e = launch_mc<8>(prm, tb, d_counts, grid, st); break;
-            case 9: e = launch_mc<9>(prm, tb, d_counts, grid, st); break;
+            case 0: e = MC_THREADS == 768 ? launch_mc<0, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<0, 640>(prm, tb, d_counts, grid, st) : launch_mc<0, 512>(prm, tb, d_counts, grid, st); break;
+            case 1: e = MC_THREADS == 768 ? launch_mc<1, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<1, 640>(prm, tb, d_counts, grid, st) : launch_mc<1, 512>(prm, tb, d_counts, grid, st); break;
+            case 2: e = MC_THREADS == 768 ? launch_mc<2, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<2, 640>(prm, tb, d_counts, grid, st) : launch_mc<2, 512>(prm, tb, d_counts, grid, st); break;
+            case 3: e = MC_THREADS == 768 ? launch_mc<3, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<3, 640>(prm, tb, d_counts, grid, st) : launch_mc<3, 512>(prm, tb, d_counts, grid, st); break;
+            case 4: e = MC_THREADS == 768 ? launch_mc<4, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<4, 640>(prm, tb, d_counts, grid, st) : launch_mc<4, 512>(prm, tb, d_counts, grid, st); break;
+            case 5: e = MC_THREADS == 768 ? launch_mc<5, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<5, 640>(prm, tb, d_counts, grid, st) : launch_mc<5, 512>(prm, tb, d_counts, grid, st); break;
+            case 6: e = MC_THREADS == 768 ? launch_mc<6, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<6, 640>(prm, tb, d_counts, grid, st) : launch_mc<6, 512>(prm, tb, d_counts, grid, st); break;
+            case 7: e = MC_THREADS == 768 ? launch_mc<7, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<7, 640>(prm, tb, d_counts, grid, st) : launch_mc<7, 512>(prm, tb, d_counts, grid, st); break;
+            case 8: e = MC_THREADS == 768 ? launch_mc<8, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<8, 640>(prm, tb, d_counts, grid, st) : launch_mc<8, 512>(prm, tb, d_counts, grid, st); break;
+            case 9: e = MC_THREADS == 768 ? launch_mc<9, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<9, 640>(prm, tb, d_counts, grid, st) : launch_mc<9, 512>(prm, tb, d_counts, grid, st); break;
             default: return cudaErrorInvalidValue;
         }
         if (e != cudaSuccess) return e;
