@@ -628,9 +628,10 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
             for (int i = 0; i < SH::STEPS; i++) {
                 if (i % 3 == 0) r = w[i / 3];
                 if (i < 2 * NR || i - 2 * NR < nb) {                     // (else: community card already on the table)
-                    const uint64_t x = (uint64_t)r * prm.m[i];           // hi = offset in [0, m), lo = the next r
-                    r = (uint32_t)x;
-                    const uint32_t jm = (uint32_t)(x >> 32) * J_MUL + (uint32_t)i * J_MUL;
+                    uint32_t hi;                                         // r * m: hi = offset in [0, m), lo = the next r
+                    asm("mul.hi.u32 %0, %1, %2;" : "=r"(hi) : "r"(r), "r"(prm.m[i]));
+                    r *= prm.m[i];
+                    const uint32_t jm = hi * J_MUL + (uint32_t)i * J_MUL;
                     unsigned char *pj = sdeck + ((jm & J_MASK) | tid4);       // word (j >> 2) of the column, byte j & 3
                     const uint32_t a = *pj;
                     *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
