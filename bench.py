@@ -31,7 +31,11 @@ ALGO_BYTES_PER_EVAL = 12         # 8 B mask in + 4 B key out
 # thread-level instructions per unit.  SURVEY 8d declared 64 / 70 / 140 / 1024 and allows lowering them "with a SASS
 # count to justify it": these are the executed warp-instructions per unit that ncu measured for the current kernels
 # (profiles/r01_v_k1_v5_ncu_full.txt, profiles/r01_z_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
-OPS = {"eval": 46, "enum": 62, "board2": 69, "mc9": 685}
+OPS = {"eval": 46, "enum": 62, "board2": 69, "mc9": 612}
+# K4 is bound by the shared-memory data pipe (one 128-byte wavefront per SM per clock): ncu counts 186 wavefronts per
+# 32 trials (profiles/r01_k4_768_ncu_full.txt: 141 without bank conflicts -- 13 deck init, 63 deal steps, 42 card
+# entries, 18 hash loads, flush -- plus 45 from the random D / V addresses of a warp sharing banks)
+MC9_SMEM_WAVEFRONTS_PER_32_TRIALS = 186
 METRIC = "7-card evals/s"
 
 
@@ -354,15 +358,26 @@ def run_ours(args):
     while mc_log2 > 28 and (1 << mc_log2) / est_rate > args.mc_budget_s:
         mc_log2 -= 1
     trials = 1 << mc_log2
+    sampler4 = ClockSampler(local)               # K4 runs for tenths of a second: its own clock sample
+    sampler4.start()
+    time.sleep(0.15)
+    sampler4.rows.clear()
     ms4 = timed_region(torch, dist, world, lambda: mc_run(trials), 1, 0)
+    clocks4 = sampler4.stop()
+    f_sm4 = (clocks4.get("sm_mhz") or sm_max_mhz) * 1e6
+    int_peak4 = sms * 128 * f_sm4
     c4 = cnt.cpu().tolist()
     rate4 = trials / (ms4 * 1e-3)
     work["config4_mc_9_seats"] = {
         "trials_per_s": rate4, "evals_per_s": 9 * rate4, "trials": trials, "log2_trials": mc_log2, "ms": ms4,
         "seat0_equity": (c4[0] + c4[9] / 2) / trials, "counts_sum_ok": all(c4[s] + c4[9 + s] + c4[18 + s] == trials for s in range(9)),
         "collective": "one NCCL all_reduce(int64 x 27)" if world > 1 else "none (1 rank)",
+        "clocks": clocks4,
         "roofline": {"bound": "int_issue", "ops_per_unit": OPS["mc9"], "achieved": rate4 * OPS["mc9"] / 1e12,
-                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate4 * OPS["mc9"] / (world * int_peak)}}
+                     "peak": world * int_peak4 / 1e12, "unit": "Tint-op/s", "frac": rate4 * OPS["mc9"] / (world * int_peak4)},
+        "roofline_smem": {"bound": "shared-memory wavefronts", "wavefronts_per_32_trials": MC9_SMEM_WAVEFRONTS_PER_32_TRIALS,
+                          "achieved": rate4 / 32 * MC9_SMEM_WAVEFRONTS_PER_32_TRIALS / 1e12, "peak": world * sms * f_sm4 / 1e12,
+                          "unit": "T wavefronts/s", "frac": rate4 / 32 * MC9_SMEM_WAVEFRONTS_PER_32_TRIALS / (world * sms * f_sm4)}}
 
     # the reference's own call site: one showdown of a full table through the host ABI (latency-bound by design)
     if rank == 0:
