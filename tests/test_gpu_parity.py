@@ -267,6 +267,31 @@ def test_equity_mc_other_shapes(gpu, oracle):
         assert rc == 0 and got == (w, t, l)
 
 
+def test_equity_mc_every_seat_shape(gpu, oracle):
+    """every (random seats, fixed seats) split of 1..9 seats -- one K4 instantiation per number of random seats -- on
+    preflop / flop / turn / river boards, counts equal to the oracle's"""
+    rng = random.Random(11)
+    api = gpu.api
+    for n_seats in range(1, 10):
+        for n_fixed in range(0, n_seats + 1):
+            n_known = rng.choice([0, 0, 3, 4, 5])
+            ids = rng.sample(range(52), 2 * n_fixed + n_known + 2)
+            fixed_at = set(rng.sample(range(n_seats), n_fixed))
+            holes, k = [], 0
+            for s in range(n_seats):
+                if s in fixed_at:
+                    holes.append(api.mask_of_ids(ids[2 * k:2 * k + 2]))
+                    k += 1
+                else:
+                    holes.append(0)
+            board = api.mask_of_ids(ids[2 * n_fixed:2 * n_fixed + n_known])
+            dead = api.mask_of_ids(ids[-2:]) if rng.random() < 0.5 else 0
+            seed, first, n = rng.getrandbits(64), rng.getrandbits(40), 12_000
+            got = api.equity_mc(holes, board, dead, seed, first, n)
+            rc, w, t, l = oracle.equity_mc(holes, board, dead, seed, first, n)
+            assert rc == 0 and got == (w, t, l), (n_seats, n_fixed, n_known)
+
+
 def test_equity_mc_converges_to_exhaustive(gpu):
     """AA vs KK by Monte Carlo vs the exact count: within 4 sigma (binomial), the tolerance the spec allows"""
     api = gpu.api
