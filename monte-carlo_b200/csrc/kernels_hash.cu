@@ -634,7 +634,9 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
                     const uint32_t jm = hi * J_MUL + (uint32_t)i * J_MUL;
                     unsigned char *pj = sdeck + ((jm & J_MASK) | tid4);       // word (j >> 2) of the column, byte j & 3
                     const uint32_t a = *pj;
-                    *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
+                    // deck[j] = deck[i]: nothing has been swapped before step 0, nobody reads after the last step
+                    if (i == 0) *pj = (unsigned char)dinit[0];
+                    else if (i < SH::STEPS - 1) *pj = dk[(i >> 2) * MC_T4 + (i & 3)];
                     card[i] = a;
                 }
                 if (i % 3 == 2 || i == SH::STEPS - 1) rej |= r < prm.thr[i / 3];   // Lemire's zone of the word's product

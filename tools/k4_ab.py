@@ -30,4 +30,4 @@ for rep in range(3):
     best = min(best, a.elapsed_time(b))
 c = cnt.tolist()
 print("K4 threads=%s: %.2f G trials/s (%.1f ms for 2^%d), win0=%d checksum=%d" % (
-    os.environ.get("MCP_K4_THREADS", "512"), (1 << log2) / best / 1e6, best, log2, c[0], sum((i + 1) * v for i, v in enumerate(c))))
+    os.environ.get("MCP_K4_THREADS", "768 (default)"), (1 << log2) / best / 1e6, best, log2, c[0], sum((i + 1) * v for i, v in enumerate(c))))
