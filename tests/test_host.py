@@ -23,6 +23,20 @@ def test_library_loads_and_exports_every_declared_symbol(pkg):
     assert L.mc_abi_version() == 1
 
 
+def test_header_is_plain_c_and_links(pkg, tmp_path):
+    """include/mcpoker.h compiles as strict C99 and a C program linked against libmcpoker.so (what a JNA / Panama /
+    cgo binding relies on) runs the device-free part of the ABI"""
+    import subprocess
+    exe = str(tmp_path / "abi_consumer")
+    libdir = os.path.dirname(pkg.engine.LIB_PATH)
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "c", "abi_consumer.c"), "-o", exe,
+                           "-L", libdir, "-lmcpoker", "-Wl,-rpath," + libdir])
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, (out.returncode, out.stdout, out.stderr)
+    assert "abi consumer ok" in out.stdout
+
+
 def test_no_gpu_means_loud_failure_not_fallback(pkg):
     import torch
     if torch.cuda.is_available():
