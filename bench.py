@@ -276,6 +276,26 @@ def run_ours(args):
     e2e_value = world * ne * e2e_steps / (e2e_ms * 1e-3)
     if rank == 0 and not torch.equal(h_keys[:check_n], keys[:check_n].cpu()):
         raise SystemExit("e2e keys differ from the device-resident run")
+    # the compact wire format of the same call: 6 B per hand (seven 6-bit card positions) instead of an 8 B mask.
+    # The hands are packed on the device here (bit shuffling only) and land in pinned host memory before the timing.
+    m_dev, h_dev = masks[:ne].clone(), torch.zeros(ne, dtype=torch.int64, device="cuda")
+    for k in range(7):
+        low = m_dev & -m_dev
+        h_dev |= (torch.log2(low.double()) + 0.5).long() << (6 * k)      # (+0.5: log2 of a power of two, rounded)
+        m_dev &= m_dev - 1
+    h_pk = torch.empty(6 * ne, dtype=torch.uint8).pin_memory()
+    h_pk.copy_(h_dev.view(torch.uint8).reshape(-1, 8)[:, :6].reshape(-1))
+    h_keys48 = torch.empty(ne, dtype=torch.int32).pin_memory()
+    del m_dev, h_dev, low
+    torch.cuda.synchronize()
+
+    def e2e48_step():
+        E.check(L.mc_eval_batch_packed48(h_pk.data_ptr(), ne, h_keys48.data_ptr()))
+
+    e2e48_ms = wall_region(torch, dist, world, e2e48_step, e2e_steps, 1)
+    e2e48_value = world * ne * e2e_steps / (e2e48_ms * 1e-3)
+    if not torch.equal(h_keys48, h_keys):
+        raise SystemExit("packed48 keys differ from the mask call")
     # the same call on pageable buffers (what a caller gets without mc_alloc_host / pinning)
     pg_masks, pg_keys = h_masks.numpy().copy(), np.empty(ne, dtype=np.uint32)
     E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
@@ -294,8 +314,11 @@ def run_ours(args):
     d2h_alone = 4 * ne / (ev[2].elapsed_time(ev[3]) * 1e-3) / 1e9
     link = {"h2d_alone_gbs": h2d_alone, "d2h_alone_gbs": d2h_alone, "h2d_in_e2e_gbs": 8 * e2e_value / world / 1e9,
             "d2h_in_e2e_gbs": 4 * e2e_value / world / 1e9, "frac_of_h2d_alone": 8 * e2e_value / world / 1e9 / h2d_alone,
+            "packed48_h2d_gbs": 6 * e2e48_value / world / 1e9, "packed48_d2h_gbs": 4 * e2e48_value / world / 1e9,
+            "packed48_frac_of_h2d_alone": 6 * e2e48_value / world / 1e9 / h2d_alone,
             "pageable_buffers_evals_per_s_per_gpu": pageable_value,
-            "note": "e2e moves 12 B per hand over the host link, both directions at once; it is bound by the H2D direction"}
+            "note": "the mask call moves 12 B per hand over the host link (8 in, 4 out), the packed48 call 10 B (6 in, 4 out), "
+                    "both directions at once; both are bound by the H2D direction (h2d_in_e2e_gbs etc. are the mask call's)"}
     del masks, keys
 
     # ---- other BASELINE configs --------------------------------------------------------------------
@@ -368,11 +391,28 @@ def run_ours(args):
     int_peak4 = sms * 128 * f_sm4
     c4 = cnt.cpu().tolist()
     rate4 = trials / (ms4 * 1e-3)
+    # the same workload through the host-buffer call a JVM makes (mc_equity_mc: hole masks in, 27 host counts out,
+    # wall clock around the call): inputs and outputs are a few hundred bytes, so end to end = the device rate
+    e2e4_log2 = min(mc_log2, 32)
+    lo4, hi4 = (1 << e2e4_log2) * rank // world, (1 << e2e4_log2) * (rank + 1) // world
+    got4 = [None]
+
+    def mc_host_call():
+        w4, t4, l4 = api.equity_mc(list(holes9), 0, 0, SEED, lo4, hi4 - lo4)
+        got4[0] = torch.tensor(w4 + t4 + l4, dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.all_reduce(got4[0], op=dist.ReduceOp.SUM)
+    ms4_host = wall_region(torch, dist, world, mc_host_call, 1, 1)
+    g4 = got4[0].cpu().tolist()
+    assert all(g4[s] + g4[9 + s] + g4[18 + s] == 1 << e2e4_log2 for s in range(9)), "mc_equity_mc counts do not add up"
     work["config4_mc_9_seats"] = {
         "trials_per_s": rate4, "evals_per_s": 9 * rate4, "trials": trials, "log2_trials": mc_log2, "ms": ms4,
         "seat0_equity": (c4[0] + c4[9] / 2) / trials, "counts_sum_ok": all(c4[s] + c4[9 + s] + c4[18 + s] == trials for s in range(9)),
         "collective": "one NCCL all_reduce(int64 x 27)" if world > 1 else "none (1 rank)",
         "clocks": clocks4,
+        "e2e": {"value": (1 << e2e4_log2) / (ms4_host * 1e-3), "unit": "trials/s", "log2_trials": e2e4_log2,
+                "call": "mc_equity_mc (host arguments in, host counts out; wall clock)",
+                "h2d_bytes_per_step": 72, "d2h_bytes_per_step": 216},
         "roofline": {"bound": "int_issue", "ops_per_unit": OPS["mc9"], "achieved": rate4 * OPS["mc9"] / 1e12,
                      "peak": world * int_peak4 / 1e12, "unit": "Tint-op/s", "frac": rate4 * OPS["mc9"] / (world * int_peak4)},
         "roofline_smem": {"bound": "shared-memory wavefronts", "wavefronts_per_32_trials": MC9_SMEM_WAVEFRONTS_PER_32_TRIALS,
@@ -486,8 +526,11 @@ def run_ours(args):
                          "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "eval7_stream_hash_kernel", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
                          "int_issue_frac": (value / world) * OPS["eval"] / int_peak, "ops_per_eval": OPS["eval"]},
-            "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
-                    "hands_per_step": ne, "call": "mc_eval7_batch (pinned host buffers, 3-stage copy/compute pipeline)",
+            "e2e": {"value": e2e48_value, "unit": "evals/s", "h2d_bytes_per_step": 6 * ne, "d2h_bytes_per_step": 4 * ne,
+                    "hands_per_step": ne,
+                    "call": "mc_eval_batch_packed48 (pinned host buffers, 6-byte hands, 3-stage copy / expand / K1 / copy pipeline)",
+                    "mask_call": {"value": e2e_value, "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
+                                  "call": "mc_eval7_batch (8-byte masks, same pipeline without the expander)"},
                     "link": link},
             "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
             "k1_variants_evals_per_s": variants, "workloads": work,

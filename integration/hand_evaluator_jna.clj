@@ -104,3 +104,24 @@
   (let [pocket    @(database/player-hand player-id (:room board))
         available (concat @(:community-cards board) pocket)]
     (key->value (eval-key available))))
+
+;; ---- additive: many hands in one call -------------------------------------------------------------------
+;; mc_eval_batch_packed48: 6 bytes per hand (seven 6-bit card positions 16*suit + rank, 0 = no card).  The call is
+;; bound by the host link, so the compact format is 4/3 of the mask format's throughput.  For large batches take the
+;; buffers from mc_alloc_host (page-locked) instead of Memory.
+(defn eval-batch
+  "hands: a seq of 5..7-card seqs -> vector of [cat hit kick] values, one per hand"
+  [hands]
+  @started
+  (let [hands (vec hands) n (count hands)
+        in (Memory. (* 6 (max n 1))) out (Memory. (* 4 (max n 1)))]
+    (dotimes [i n]
+      (let [cards (vec (hands i))
+            ranks (mapv rank-of cards)
+            sids  (resuit-repeats (suit-ids cards) ranks)
+            h     (reduce (fn [acc k] (bit-or acc (bit-shift-left (+ (* 16 (long (sids k))) (long (ranks k))) (* 6 k))))
+                          0 (range (count cards)))]
+        (.setInt in (* 6 i) (unchecked-int h))
+        (.setShort in (+ 4 (* 6 i)) (unchecked-short (bit-shift-right h 32)))))
+    (check (call-int "mc_eval_batch_packed48" in (long n) out))
+    (mapv #(key->value (Integer/toUnsignedLong (.getInt out (* 4 %)))) (range n))))

@@ -54,6 +54,38 @@ def eval7_batch(masks, key_format=E.KEY_NIBBLE, out=None):
     return keys
 
 
+def pack48(masks):
+    """uint64 card masks (<= 7 cards each) -> the 6-byte wire format of mc_eval_batch_packed48 (host bit shuffling
+    in numpy: seven 6-bit card positions per hand, lowest card first, unused fields 0)"""
+    m = np.ascontiguousarray(masks, dtype=np.uint64).copy()
+    h = np.zeros(m.shape[0], dtype=np.uint64)
+    one = np.uint64(1)
+    for k in range(7):
+        low = m & (~m + one)                                   # lowest set bit (0 when the hand is used up)
+        pos = np.zeros(m.shape[0], dtype=np.uint64)
+        for b in (32, 16, 8, 4, 2, 1):                         # log2 of a power of two, branch-free
+            big = (low >> np.uint64(b)) != 0
+            pos += np.where(big, np.uint64(b), np.uint64(0))
+            low = np.where(big, low >> np.uint64(b), low)
+        h |= pos << np.uint64(6 * k)
+        m &= m - one
+    if np.any(m):
+        raise ValueError("a hand holds more than 7 cards")
+    return np.ascontiguousarray(h.view(np.uint8).reshape(-1, 8)[:, :6]).reshape(-1)
+
+
+def eval_batch_packed48(packed, out=None):
+    """packed: uint8 array of 6*n bytes (pack48) -> nibble keys"""
+    E.ensure_init()
+    packed = np.ascontiguousarray(packed, dtype=np.uint8)
+    if packed.size % 6:
+        raise ValueError("packed48 hands are 6 bytes each")
+    n = packed.size // 6
+    keys = out if out is not None else np.empty(n, dtype=np.uint32)
+    E.check(E.lib().mc_eval_batch_packed48(packed.ctypes.data, n, keys.ctypes.data))
+    return keys
+
+
 def random_hands(seed, first, n, n_cards=7):
     E.ensure_init()
     out = np.empty(n, dtype=np.uint64)

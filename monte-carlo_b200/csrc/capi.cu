@@ -43,6 +43,7 @@ struct DevCtx {
     cudaStream_t slot_stream[N_SLOTS] = {};
     uint64_t *d_in[N_SLOTS] = {};
     uint32_t *d_out[N_SLOTS] = {};
+    unsigned char *d_pk[N_SLOTS] = {};            // packed48 input stages (6 B per hand), allocated on first use
     unsigned long long *d_small = nullptr;        // SMALL_WORDS x u64 scratch
     unsigned long long *h_small = nullptr;        // pinned mirror (mapped)
     unsigned long long *hd_small = nullptr;       // the device's address of h_small
@@ -61,6 +62,7 @@ struct DevCtx {
         for (int i = 0; i < N_SLOTS; i++) {
             if (d_in[i]) cudaFree(d_in[i]);
             if (d_out[i]) cudaFree(d_out[i]);
+            if (d_pk[i]) cudaFree(d_pk[i]);
             if (slot_stream[i]) cudaStreamDestroy(slot_stream[i]);
         }
         if (d_small) cudaFree(d_small);
@@ -232,6 +234,12 @@ int ensure_slots(DevCtx &c) {
     return MC_OK;
 }
 
+int ensure_packed_slots(DevCtx &c) {
+    if (c.d_pk[0]) return MC_OK;
+    for (int i = 0; i < N_SLOTS; i++) CU(cudaMalloc(&c.d_pk[i], SLOT_HANDS * 6));
+    return MC_OK;
+}
+
 int check_equity_args(const uint64_t *hole_masks, int n_seats, uint64_t board, uint64_t dead, bool allow_random,
                       EquityArgs *out, int *need_cards) {
     if (!hole_masks) return fail(MC_ERR_INVALID, "hole_masks is null");
@@ -338,21 +346,30 @@ int mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void
     return mc_eval7_batch_dev_fmt(d_masks, n, d_keys, MC_KEY_NIBBLE, stream);
 }
 
-int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_format) {
+namespace {
+// host buffers -> keys.  The input is either masks (8 B per hand) or packed48 hands (6 B per hand, expanded to masks
+// on the device).  Contiguous slice per device, each streamed through N_SLOTS staging buffers on their own streams so
+// the H2D copy of stage i+1, the kernel(s) of stage i and the D2H copy of stage i-1 overlap.
+int eval_batch_host(const void *in, bool packed48, size_t n, uint32_t *keys, int key_format) {
     int rc = need_init();
     if (rc) return rc;
     if (n == 0) return MC_OK;
-    if (!masks || !keys) return fail(MC_ERR_INVALID, "null buffer");
+    if (!in || !keys) return fail(MC_ERR_INVALID, "null buffer");
+    const size_t in_bytes = packed48 ? 6 : sizeof(uint64_t);
+    const unsigned char *src = static_cast<const unsigned char *>(in);
     const int nd = (int)g_ctx.size();
     std::vector<std::unique_lock<std::mutex>> locks;
     for (auto &c : g_ctx) locks.emplace_back(c->mu);
-    // contiguous slice per device, each streamed through N_SLOTS staging buffers on their own streams so the
-    // H2D copy of stage i+1, the kernel of stage i and the D2H copy of stage i-1 overlap
     const size_t per_dev = (n + nd - 1) / nd;
     std::vector<size_t> pos(nd), end(nd);
     for (int d = 0; d < nd; d++) {
         pos[d] = std::min(n, per_dev * d); end[d] = std::min(n, pos[d] + per_dev);
-        if (end[d] > pos[d]) { CU(cudaSetDevice(g_ctx[d]->device)); rc = ensure_slots(*g_ctx[d]); if (rc) return rc; }
+        if (end[d] > pos[d]) {
+            CU(cudaSetDevice(g_ctx[d]->device));
+            rc = ensure_slots(*g_ctx[d]);
+            if (!rc && packed48) rc = ensure_packed_slots(*g_ctx[d]);
+            if (rc) return rc;
+        }
     }
     bool more = true;
     for (size_t round = 0; more; round++) {
@@ -363,7 +380,12 @@ int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_
             const int s = (int)(round % N_SLOTS);
             const size_t cnt = std::min(SLOT_HANDS, end[d] - pos[d]);
             CU(cudaSetDevice(c.device));
-            CU(cudaMemcpyAsync(c.d_in[s], masks + pos[d], cnt * sizeof(uint64_t), cudaMemcpyHostToDevice, c.slot_stream[s]));
+            if (packed48) {
+                CU(cudaMemcpyAsync(c.d_pk[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
+                CU(launch_unpack48(c.d_pk[s], cnt, c.d_in[s], c.info, c.slot_stream[s]));
+            } else {
+                CU(cudaMemcpyAsync(c.d_in[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
+            }
             CU(launch_k1(c.d_in[s], cnt, c.d_out[s], key_format, c.info, &c.tb, c.slot_stream[s]));
             CU(cudaMemcpyAsync(keys + pos[d], c.d_out[s], cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.slot_stream[s]));
             pos[d] += cnt;
@@ -377,6 +399,14 @@ int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_
         for (int s = 0; s < N_SLOTS; s++) CU(cudaStreamSynchronize(c.slot_stream[s]));
     }
     return MC_OK;
+}
+}  // namespace
+
+int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_format) {
+    return eval_batch_host(masks, false, n, keys, key_format);
+}
+int mc_eval_batch_packed48(const uint8_t *hands, size_t n, uint32_t *keys) {
+    return eval_batch_host(hands, true, n, keys, MC_KEY_NIBBLE);
 }
 void *mc_alloc_host(size_t bytes) {
     if (need_init()) return nullptr;

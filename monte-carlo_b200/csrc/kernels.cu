@@ -289,6 +289,53 @@ cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_c
 }
 
 // ---------------------------------------------------------------------------------------------------
+// packed48 -> masks (mc_eval_batch_packed48): a hand is a little-endian 48-bit field of seven 6-bit card positions
+// (16 * suit + rank, the bit mc_card_bit sets; 0 = no card, so 5- and 6-card hands fit too).  6 B per hand cross
+// the host link instead of 8.  A thread expands four hands: three 8-byte loads, two 16-byte stores.  A repeated
+// card or a set bit above bit 41 yields the mask 1 (not a card), which every K1 variant maps to MC_KEY_INVALID.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t expand48(uint64_t h) {
+    uint64_t m = 0, dup = h >> 42;
+#pragma unroll
+    for (int k = 0; k < 7; k++) {
+        const uint32_t f = (uint32_t)(h >> (6 * k)) & 63u;
+        const uint64_t bit = f ? 1ull << f : 0ull;
+        dup |= m & bit;
+        m |= bit;
+    }
+    return dup ? 1ull : m;
+}
+__global__ void __launch_bounds__(256)
+unpack48_kernel(const unsigned char *__restrict__ pk, size_t n, uint64_t *__restrict__ masks) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x, groups = n / 4;
+    constexpr uint64_t M48 = 0xFFFFFFFFFFFFull;
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += stride) {
+        const uint64_t *p = reinterpret_cast<const uint64_t *>(pk + 24 * g);
+        const uint64_t a = __ldcs(p), b = __ldcs(p + 1), c = __ldcs(p + 2);
+        ulonglong2 lo, hi;
+        lo.x = expand48(a & M48);
+        lo.y = expand48((a >> 48 | b << 16) & M48);
+        hi.x = expand48((b >> 32 | c << 32) & M48);
+        hi.y = expand48(c >> 16);
+        ulonglong2 *o = reinterpret_cast<ulonglong2 *>(masks + 4 * g);
+        o[0] = lo; o[1] = hi;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {                  // the last n % 4 hands, byte by byte
+        const size_t i = 4 * groups + threadIdx.x;
+        uint64_t h = 0;
+        for (int k = 0; k < 6; k++) h |= (uint64_t)pk[6 * i + k] << (8 * k);
+        masks[i] = expand48(h);
+    }
+}
+// d_packed 8-byte aligned, d_masks 16-byte aligned
+cudaError_t launch_unpack48(const unsigned char *d_packed, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    size_t want = (n / 4 + 255) / 256 + 1, cap = (size_t)di.sm_count * 8;
+    unpack48_kernel<<<(int)(want > cap ? cap : want), 256, 0, st>>>(d_packed, n, d_masks);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
 // single showdown: one warp, lane s = seat s (end-game ranking + group-winners, gameplay.clj:118-132)
 // ---------------------------------------------------------------------------------------------------
 __global__ void showdown_kernel(const __grid_constant__ EquityArgs a, uint32_t *__restrict__ out, uint32_t ticket) {

@@ -26,6 +26,7 @@ cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t
                                      const StreamHash &S, const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,
                                 const DeviceInfo &di, cudaStream_t st);
+cudaError_t launch_unpack48(const unsigned char *d_packed, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st);
 struct EquityArgs {
     uint64_t hole[MAX_SEATS];   // 0 = random seat (Monte Carlo only)
     uint64_t board;             // known community cards

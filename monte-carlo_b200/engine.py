@@ -18,7 +18,7 @@ N_CLASSES = 169
 EXPORTS = [
     "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version",
     "mc_card_bit", "mc_key_packed_to_nibble", "mc_key_decode",
-    "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
+    "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval_batch_packed48", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
     "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_random_hands", "mc_random_hands_dev",
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
@@ -69,6 +69,7 @@ def lib():
     L.mc_eval_cards.argtypes = [P(i32), P(i32), C.c_int, P(u32)]
     L.mc_eval7_batch.argtypes = [vp, sz, vp]
     L.mc_eval7_batch_fmt.argtypes = [vp, sz, vp, C.c_int]
+    L.mc_eval_batch_packed48.argtypes = [vp, sz, vp]
     L.mc_eval7_batch_dev.argtypes = [vp, sz, vp, vp]
     L.mc_eval7_batch_dev_fmt.argtypes = [vp, sz, vp, C.c_int, vp]
     L.mc_showdown.argtypes = [u64, P(u64), C.c_int, P(u32), P(u32)]

@@ -152,6 +152,34 @@ def test_eval7_batch_from_library_pinned_buffers(gpu, oracle):
     assert L.mc_free_host(pm) == 0 and L.mc_free_host(pk) == 0 and L.mc_free_host(None) == 0
 
 
+def test_eval_batch_packed48_equals_mask_path_and_oracle(gpu, oracle):
+    """the 6-byte wire format (seven 6-bit card positions) gives the keys of the mask path: 7-, 6- and 5-card hands,
+    ragged sizes around the 4-hand groups of the expander and across pipeline stages"""
+    api = gpu.api
+    for n_cards, n in ((7, 1_000_003), (6, 40_001), (5, 40_002), (7, 1), (7, 2), (7, 3), (7, 5), (7, (1 << 22) + 7)):
+        masks = oracle.random_hands(SEED + n_cards, 11, n, n_cards)
+        keys = api.eval_batch_packed48(api.pack48(masks))
+        assert np.array_equal(keys, oracle.eval_batch(masks, 0)), (n_cards, n)
+    # the ace-low hands of the reference's own tests (rank 1) travel too
+    m = np.array([sum(1 << (16 * s + r) for s, r in zip((0, 1, 2, 3, 0), (1, 2, 3, 4, 5)))], dtype=np.uint64)
+    assert np.array_equal(api.eval_batch_packed48(api.pack48(m)), oracle.eval_batch(m, 0))
+
+
+def test_eval_batch_packed48_rejects_malformed_hands(gpu):
+    api = gpu.api
+
+    def pk(fields, high=0):
+        h = sum(f << (6 * k) for k, f in enumerate(fields)) | high << 42
+        return np.frombuffer(int(h).to_bytes(8, "little")[:6], dtype=np.uint8)
+    good = [2, 3, 4, 5, 6, 18, 19]
+    cases = [(pk(good), False), (pk(good[:5] + [0, 0]), False), (pk([2, 2, 4, 5, 6, 18, 19]), True),
+             (pk([0] * 7), True), (pk(good[:4] + [0] * 3), True), (pk(good, high=1), True),
+             (pk([16, 3, 4, 5, 6, 18, 19]), True), (pk([15, 3, 4, 5, 6, 18, 19]), True)]   # bits 0 / 15 of a lane are not cards
+    keys = api.eval_batch_packed48(np.concatenate([c for c, _ in cases]))
+    for k, (_, bad) in zip(keys, cases):
+        assert (int(k) == 0xFFFFFFFF) == bad
+
+
 def test_k1_every_seven_card_hand_key_by_key(gpu, oracle):
     """BASELINE target: 100 % bit-exact rank agreement on all 133,784,560 seven-card hands, key by key, through the
     host-buffer ABI call (the K1 hash kernel for these batch sizes) against the oracle's direct evaluator"""

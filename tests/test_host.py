@@ -37,6 +37,28 @@ def test_header_is_plain_c_and_links(pkg, tmp_path):
     assert "abi consumer ok" in out.stdout
 
 
+def test_pack48_wire_format(pkg, oracle):
+    """api.pack48: 6 bytes per hand, seven 6-bit card positions lowest card first, unused fields 0; decodes back"""
+    import numpy as np
+    for n_cards in (5, 6, 7):
+        masks = oracle.random_hands(3, 0, 5000, n_cards)
+        p = pkg.api.pack48(masks)
+        assert p.dtype == np.uint8 and p.shape == (6 * 5000,)
+        b = p.reshape(-1, 6).astype(np.uint64)
+        h = sum(b[:, k] << np.uint64(8 * k) for k in range(6))
+        back = np.zeros(5000, dtype=np.uint64)
+        for k in range(7):
+            f = (h >> np.uint64(6 * k)) & np.uint64(63)
+            assert np.all((f != 0) == (k < n_cards))
+            back |= np.where(f != 0, np.uint64(1) << f, np.uint64(0))
+        assert np.array_equal(back, masks)
+    first = int(masks[0])
+    lowest = (first & -first).bit_length() - 1
+    assert int(p[0]) & 63 == lowest
+    with pytest.raises(ValueError):
+        pkg.api.pack48(np.array([0xFF00FF], dtype=np.uint64))
+
+
 def test_no_gpu_means_loud_failure_not_fallback(pkg):
     import torch
     if torch.cuda.is_available():
