@@ -347,6 +347,14 @@ int mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void
 }
 
 namespace {
+size_t stage_hands() {        // hands per pipeline stage of the host-buffer calls (<= SLOT_HANDS, the staging buffers' size)
+    static const size_t v = [] {
+        const char *e = getenv("MCP_STAGE_LOG2");
+        const int l = e ? atoi(e) : 0;
+        return (l >= 12 && l <= 22) ? (size_t)1 << l : SLOT_HANDS;
+    }();
+    return v;
+}
 // host buffers -> keys.  The input is either masks (8 B per hand) or packed48 hands (6 B per hand, expanded to masks
 // on the device).  Contiguous slice per device, each streamed through N_SLOTS staging buffers on their own streams so
 // the H2D copy of stage i+1, the kernel(s) of stage i and the D2H copy of stage i-1 overlap.
@@ -378,7 +386,7 @@ int eval_batch_host(const void *in, bool packed48, size_t n, uint32_t *keys, int
             if (pos[d] >= end[d]) continue;
             DevCtx &c = *g_ctx[d];
             const int s = (int)(round % N_SLOTS);
-            const size_t cnt = std::min(SLOT_HANDS, end[d] - pos[d]);
+            const size_t cnt = std::min(stage_hands(), end[d] - pos[d]);
             CU(cudaSetDevice(c.device));
             if (packed48) {
                 CU(cudaMemcpyAsync(c.d_pk[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));

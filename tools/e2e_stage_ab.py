@@ -1,0 +1,43 @@
+"""A/B of the pipeline stage size of the host-buffer calls (MCP_STAGE_LOG2=12..22): 2^26 hands, pinned buffers."""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+import mcb200_loader  # noqa: E402
+
+pkg = mcb200_loader.load()
+E = pkg.engine
+torch.cuda.set_device(0)
+E.init(devices=[0])
+L = E.lib()
+n = 1 << 26
+st = torch.cuda.current_stream().cuda_stream
+d = torch.empty(n, dtype=torch.int64, device="cuda")
+E.check(L.mc_random_hands_dev(0x5EED5EED, 0, n, 7, d.data_ptr(), st))
+h_masks = torch.empty(n, dtype=torch.int64).pin_memory()
+h_masks.copy_(d)
+m, h = d.clone(), torch.zeros(n, dtype=torch.int64, device="cuda")
+for k in range(7):
+    low = m & -m
+    h |= (torch.log2(low.double()) + 0.5).long() << (6 * k)
+    m &= m - 1
+h_pk = torch.empty(6 * n, dtype=torch.uint8).pin_memory()
+h_pk.copy_(h.view(torch.uint8).reshape(-1, 8)[:, :6].reshape(-1))
+k1 = torch.empty(n, dtype=torch.int32).pin_memory()
+k2 = torch.empty(n, dtype=torch.int32).pin_memory()
+torch.cuda.synchronize()
+res = {}
+for name, fn in (("mask", lambda: E.check(L.mc_eval7_batch(h_masks.data_ptr(), n, k1.data_ptr()))),
+                 ("packed48", lambda: E.check(L.mc_eval_batch_packed48(h_pk.data_ptr(), n, k2.data_ptr())))):
+    fn()
+    best = 1e9
+    for _ in range(5):
+        t0 = time.perf_counter()
+        fn()
+        best = min(best, time.perf_counter() - t0)
+    res[name] = n / best / 1e9
+print("stage 2^%s: mask %.2f G evals/s, packed48 %.2f G evals/s, equal %s" % (
+    os.environ.get("MCP_STAGE_LOG2", "22"), res["mask"], res["packed48"], torch.equal(k1, k2)))
