@@ -15,6 +15,7 @@ import argparse
 import ctypes as C
 import json
 import os
+import re
 import subprocess
 import sys
 import threading
@@ -321,6 +322,21 @@ def run_ours(args):
                     "both directions at once; both are bound by the H2D direction (h2d_in_e2e_gbs etc. are the mask call's)"}
     del masks, keys
 
+    # ---- integer pipes of this GPU, measured in this run: thread-ops per clock per SM ----------------
+    pipes = None
+    pb = os.path.join(ROOT, "tools", "pipebench")
+    if rank == 0 and os.path.exists(pb):
+        try:
+            txt = subprocess.run([pb], capture_output=True, text=True, timeout=60).stdout
+            pick = {"LOP3": "lop3", "IADD": "iadd", "IMAD": "imad", "IMAD.HI (mul.hi)": "imad_hi", "POPC": "popc", "SHF": "shf",
+                    "LOP3+IMAD mix": "lop3_imad_mix", "LDS random (8192 words)": "lds_random_words"}
+            pipes = {"unit": "thread-ops/clk/SM", "tool": "tools/pipebench.cu"}
+            for label, num in re.findall(r"^(.*?)\s+([0-9.]+) thread-ops/clk/SM", txt, flags=re.M):
+                if label in pick:
+                    pipes[pick[label]] = float(num)
+        except Exception as ex:          # the probe is a report, never a reason to lose the bench line
+            pipes = {"error": str(ex)}
+
     # ---- other BASELINE configs --------------------------------------------------------------------
     work = {}
     f_sm = (clocks.get("sm_mhz") or sm_max_mhz) * 1e6
@@ -533,7 +549,7 @@ def run_ours(args):
                                   "call": "mc_eval7_batch (8-byte masks, same pipeline without the expander)"},
                     "link": link},
             "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
-            "k1_variants_evals_per_s": variants, "workloads": work,
+            "k1_variants_evals_per_s": variants, "int_pipes_measured": pipes, "workloads": work,
         }
         if cpu:
             line["cpu_baseline"] = cpu
