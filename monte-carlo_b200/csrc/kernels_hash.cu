@@ -724,9 +724,14 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 }
 
 static size_t mc_smem(int threads) { return 13 * 4 * (size_t)(threads <= 512 ? 512 : 1024) + 64 * MC_REP * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
-static int mc_threads() {
-    static const int t = [] { const char *e = getenv("MCP_K4_THREADS"); const int v = e ? atoi(e) : 0; return v == 512 || v == 640 ? v : 768; }();   // A/B knob of tools/k4_ab.py
-    return t;
+// threads per block by number of random seats: tables of up to three random seats fit 64 registers and run 1024
+// threads, the others 768 x 80 registers.  MCP_K4_THREADS=512|768|1024 overrides (A/B knob of tools/k4_ab.py; 1024 only
+// where the variant exists).
+static int mc_threads(int nr) {
+    static const int forced = [] { const char *e = getenv("MCP_K4_THREADS"); const int v = e ? atoi(e) : 0; return v == 512 || v == 768 || v == 1024 ? v : 0; }();
+    if (forced == 1024) return nr <= 3 ? 1024 : 768;
+    if (forced) return forced;
+    return nr <= 3 ? 1024 : 768;
 }
 
 template <int NR, int MC_THREADS>
@@ -767,23 +772,23 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
         prm.thr[w] = (uint32_t)((1ull << 32) % prod);
     }
     const int grid = di.sm_count;
-    const int MC_THREADS = mc_threads();
+    const int MC_THREADS = mc_threads(nr);
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
     for (uint64_t done = 0; done < n_trials; done += per_launch) {
         prm.first = first_trial + done;
         prm.count = (n_trials - done) < per_launch ? (n_trials - done) : per_launch;
         cudaError_t e;
         switch (nr) {
-            case 0: e = MC_THREADS == 768 ? launch_mc<0, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<0, 640>(prm, tb, d_counts, grid, st) : launch_mc<0, 512>(prm, tb, d_counts, grid, st); break;
-            case 1: e = MC_THREADS == 768 ? launch_mc<1, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<1, 640>(prm, tb, d_counts, grid, st) : launch_mc<1, 512>(prm, tb, d_counts, grid, st); break;
-            case 2: e = MC_THREADS == 768 ? launch_mc<2, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<2, 640>(prm, tb, d_counts, grid, st) : launch_mc<2, 512>(prm, tb, d_counts, grid, st); break;
-            case 3: e = MC_THREADS == 768 ? launch_mc<3, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<3, 640>(prm, tb, d_counts, grid, st) : launch_mc<3, 512>(prm, tb, d_counts, grid, st); break;
-            case 4: e = MC_THREADS == 768 ? launch_mc<4, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<4, 640>(prm, tb, d_counts, grid, st) : launch_mc<4, 512>(prm, tb, d_counts, grid, st); break;
-            case 5: e = MC_THREADS == 768 ? launch_mc<5, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<5, 640>(prm, tb, d_counts, grid, st) : launch_mc<5, 512>(prm, tb, d_counts, grid, st); break;
-            case 6: e = MC_THREADS == 768 ? launch_mc<6, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<6, 640>(prm, tb, d_counts, grid, st) : launch_mc<6, 512>(prm, tb, d_counts, grid, st); break;
-            case 7: e = MC_THREADS == 768 ? launch_mc<7, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<7, 640>(prm, tb, d_counts, grid, st) : launch_mc<7, 512>(prm, tb, d_counts, grid, st); break;
-            case 8: e = MC_THREADS == 768 ? launch_mc<8, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<8, 640>(prm, tb, d_counts, grid, st) : launch_mc<8, 512>(prm, tb, d_counts, grid, st); break;
-            case 9: e = MC_THREADS == 768 ? launch_mc<9, 768>(prm, tb, d_counts, grid, st) : MC_THREADS == 640 ? launch_mc<9, 640>(prm, tb, d_counts, grid, st) : launch_mc<9, 512>(prm, tb, d_counts, grid, st); break;
+            case 0: e = MC_THREADS == 1024 ? launch_mc<0, 1024>(prm, tb, d_counts, grid, st) : MC_THREADS == 768 ? launch_mc<0, 768>(prm, tb, d_counts, grid, st) : launch_mc<0, 512>(prm, tb, d_counts, grid, st); break;
+            case 1: e = MC_THREADS == 1024 ? launch_mc<1, 1024>(prm, tb, d_counts, grid, st) : MC_THREADS == 768 ? launch_mc<1, 768>(prm, tb, d_counts, grid, st) : launch_mc<1, 512>(prm, tb, d_counts, grid, st); break;
+            case 2: e = MC_THREADS == 1024 ? launch_mc<2, 1024>(prm, tb, d_counts, grid, st) : MC_THREADS == 768 ? launch_mc<2, 768>(prm, tb, d_counts, grid, st) : launch_mc<2, 512>(prm, tb, d_counts, grid, st); break;
+            case 3: e = MC_THREADS == 1024 ? launch_mc<3, 1024>(prm, tb, d_counts, grid, st) : MC_THREADS == 768 ? launch_mc<3, 768>(prm, tb, d_counts, grid, st) : launch_mc<3, 512>(prm, tb, d_counts, grid, st); break;
+            case 4: e = MC_THREADS == 768 ? launch_mc<4, 768>(prm, tb, d_counts, grid, st) : launch_mc<4, 512>(prm, tb, d_counts, grid, st); break;
+            case 5: e = MC_THREADS == 768 ? launch_mc<5, 768>(prm, tb, d_counts, grid, st) : launch_mc<5, 512>(prm, tb, d_counts, grid, st); break;
+            case 6: e = MC_THREADS == 768 ? launch_mc<6, 768>(prm, tb, d_counts, grid, st) : launch_mc<6, 512>(prm, tb, d_counts, grid, st); break;
+            case 7: e = MC_THREADS == 768 ? launch_mc<7, 768>(prm, tb, d_counts, grid, st) : launch_mc<7, 512>(prm, tb, d_counts, grid, st); break;
+            case 8: e = MC_THREADS == 768 ? launch_mc<8, 768>(prm, tb, d_counts, grid, st) : launch_mc<8, 512>(prm, tb, d_counts, grid, st); break;
+            case 9: e = MC_THREADS == 768 ? launch_mc<9, 768>(prm, tb, d_counts, grid, st) : launch_mc<9, 512>(prm, tb, d_counts, grid, st); break;
             default: return cudaErrorInvalidValue;
         }
         if (e != cudaSuccess) return e;

@@ -1,4 +1,4 @@
-"""A/B of the K4 launch shapes (MCP_K4_THREADS=512|768): 9 seats (1 fixed + 8 random), 2^log2 trials, CUDA events.
+"""A/B of the K4 launch shapes (MCP_K4_THREADS=512|768|1024): 9 seats (1 fixed + 8 random), 2^log2 trials, CUDA events.
 usage: MCP_K4_THREADS=768 python tools/k4_ab.py [log2_trials]   -- prints G trials/s and the 27 counts' checksum"""
 import ctypes as C
 import os
