@@ -532,7 +532,7 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
 // access of a warp is conflict-free whatever the indices, and the byte offset of position j is
 // (j * (S + 1) & (15 * 4S | 3)) | 4 * tid.  768 threads x 80 registers per SM: the 52 KB of decks, the 8 KB card
 // table and the 164 KB hash blob fill the 227 KB of shared memory (measured 512 / 640 / 768 threads: 40.7 / 42.8 /
-// 43.9 G trials/s, tools/k4_ab.py).
+// 43.9 G trials/s, tools/k4_ab.py); tables of up to three random seats need <= 64 registers and run 1024 threads.
 // Seats are processed in kernel order: random seats first (cards q and q + NR of the deal, the order of
 // deal-hand gameplay.clj:63-75), then the fixed seats; seat_of[] maps back to the caller's seat numbers.
 // A card's table entry is {premultiplied rank key, suit-counter increment | rank bit << 16}: the low half of the
