@@ -136,8 +136,10 @@ struct EqxHashParams {
     uint4 live[LIVE_MAX];               // ascending bit position; entries >= n_live are zero
 };
 
+template <int NS> constexpr int eqx_threads() { return NS == 2 ? 1024 : HASH_THREADS; }   // heads-up needs <= 51 registers
+
 template <int K, int NS>
-__global__ void __launch_bounds__(HASH_THREADS, 1)
+__global__ void __launch_bounds__(eqx_threads<NS>(), 1)
 equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob *__restrict__ g_blob,
                        long long *__restrict__ d_counts) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -199,7 +201,7 @@ static cudaError_t launch_eqx(const EqxHashParams &prm, const HashBlob *blob, lo
     auto kern = equity_exh_hash_kernel<K, NS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
     if (e != cudaSuccess) return e;
-    kern<<<grid, HASH_THREADS, eqx_smem(), st>>>(prm, blob, d_counts);
+    kern<<<grid, eqx_threads<NS>(), eqx_smem(), st>>>(prm, blob, d_counts);
     return cudaGetLastError();
 }
 
@@ -218,9 +220,10 @@ cudaError_t launch_equity_exhaustive_hash(const EquityArgs &a, uint64_t first_bo
     prm.first = first_board; prm.count = n_boards; prm.n_seats = a.n_seats;
     fill_live(DECK_MASK & ~used, tb.h_card, prm.live, &prm.n_live);
     const int K = 5 - __builtin_popcountll(a.board);
-    uint64_t want = (n_boards + HASH_THREADS - 1) / HASH_THREADS;
-    const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
     const bool two = a.n_seats == 2;
+    const uint64_t tpb = two ? eqx_threads<2>() : eqx_threads<MAX_SEATS>();
+    uint64_t want = (n_boards + tpb - 1) / tpb;
+    const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
 #define EQX_CASE(k) case k: return two ? launch_eqx<k, 2>(prm, tb.d_blob, d_counts, grid, st) : launch_eqx<k, MAX_SEATS>(prm, tb.d_blob, d_counts, grid, st)
     switch (K) {
         EQX_CASE(0); EQX_CASE(1); EQX_CASE(2); EQX_CASE(3); EQX_CASE(4); EQX_CASE(5);
