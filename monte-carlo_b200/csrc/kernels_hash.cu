@@ -574,11 +574,14 @@ __device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t 
     o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
 }
 
-template <int NR, int MC_THREADS>
+// NFX = fixed seats compiled in: MAX_SEATS - NR in general, 1 for the tables with at most one fixed seat (their
+// showdown then has NR + 1 slots instead of nine)
+template <int NR, int MC_THREADS, int NFX>
 __global__ void __launch_bounds__(MC_THREADS, 1)
 equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__restrict__ g_blob,
                     const CardKey *__restrict__ g_card, long long *__restrict__ d_counts) {
     using SH = McShape<NR>;
+    constexpr int NSLOT = NR + NFX;                                                          // seats compiled in
     constexpr int MC_STRIDE = MC_THREADS <= 512 ? 512 : 1024;                                // deck column stride in words (power of two)
     constexpr int MC_T4 = 4 * MC_STRIDE;
     constexpr uint32_t J_MUL = MC_STRIDE + 1, J_MASK = (15u * MC_T4) | 3u;                   // j * J_MUL & J_MASK = (j >> 2) * MC_T4 + (j & 3)
@@ -609,9 +612,9 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     uint32_t dinit[13];
 #pragma unroll
     for (int k = 0; k < 13; k++) dinit[k] = prm.deck_init[k];
-    uint32_t acc[MAX_SEATS];                  // per kernel seat: wins << 16 | times at the maximum
+    uint32_t acc[NSLOT > 0 ? NSLOT : 1];                  // per kernel seat: wins << 16 | times at the maximum
 #pragma unroll
-    for (int s = 0; s < MAX_SEATS; s++) acc[s] = 0;
+    for (int s = 0; s < NSLOT; s++) acc[s] = 0;
     uint32_t units = 0;
 
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
@@ -662,7 +665,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 #pragma unroll
         for (int k = 0; k < 5; k++) if (k < nb) lb |= (eb[k].y & cbit) ? (eb[k].y >> 16) : 0u;
 
-        uint32_t key[MAX_SEATS];
+        uint32_t key[NSLOT > 0 ? NSLOT : 1];
 #pragma unroll
         for (int q = 0; q < NR; q++) {
             const uint2 e1 = rep_of(card[q]), e2 = rep_of(card[q + NR]);
@@ -676,7 +679,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
             key[q] = k;
         }
 #pragma unroll
-        for (int s = 0; s < MAX_SEATS - NR; s++) {
+        for (int s = 0; s < NFX; s++) {
             key[NR + s] = 0;
             if (s < nf) {
                 const uint32_t t = b.t + prm.h_t[s], sn = b.sn + prm.h_sn[s];
@@ -692,24 +695,24 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         // key + (0x10000 - best) carries into bit 16 exactly for the seats at the maximum: no compares, no predicates
         uint32_t best = 0;
 #pragma unroll
-        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) best = max(best, key[s]);
+        for (int s = 0; s < NSLOT; s++) if (s < NR || s - NR < nf) best = max(best, key[s]);
         const uint32_t cb = 0x10000u - best;
-        uint32_t at[MAX_SEATS], nbest = 0;
+        uint32_t at[NSLOT > 0 ? NSLOT : 1], nbest = 0;
 #pragma unroll
-        for (int s = 0; s < MAX_SEATS; s++) {
+        for (int s = 0; s < NSLOT; s++) {
             at[s] = 0;
             if (s < NR || s - NR < nf) { at[s] = (key[s] + cb) >> 16; nbest += at[s]; }
         }
         const uint32_t inc = nbest == 1 ? 0x10001u : 1u;
 #pragma unroll
-        for (int s = 0; s < MAX_SEATS; s++) if (s < NR || s - NR < nf) acc[s] += at[s] * inc;
+        for (int s = 0; s < NSLOT; s++) if (s < NR || s - NR < nf) acc[s] += at[s] * inc;
         units++;
     }
 
     // per-thread 16-bit halves (the launcher keeps a thread below 65536 trials) -> warp -> block -> global
     const int lane = threadIdx.x & 31, n_seats = NR + nf;
 #pragma unroll
-    for (int s = 0; s < MAX_SEATS; s++) if (s < n_seats) {
+    for (int s = 0; s < NSLOT; s++) if (s < n_seats) {
         const uint32_t w = warp_sum(acc[s] >> 16), e = warp_sum(acc[s] & 0xFFFFu);
         if (lane == 0) { if (w) atomicAdd(&sred[s], (unsigned long long)w); if (e) atomicAdd(&sred[9 + s], (unsigned long long)e); }
     }
@@ -737,13 +740,21 @@ static int mc_threads(int nr) {
     return nr <= 3 ? 1024 : 768;
 }
 
-template <int NR, int MC_THREADS>
-static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
-    auto kern = equity_mc_fy_kernel<NR, MC_THREADS>;
+template <int NR, int MC_THREADS, int NFX>
+static cudaError_t launch_mc_nfx(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
+    auto kern = equity_mc_fy_kernel<NR, MC_THREADS, NFX>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mc_smem(MC_THREADS));
     if (e != cudaSuccess) return e;
     kern<<<grid, MC_THREADS, mc_smem(MC_THREADS), st>>>(prm, tb.d_blob, tb.d_card, d_counts);
     return cudaGetLastError();
+}
+template <int NR, int MC_THREADS>
+static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
+    constexpr int NF_ALL = MAX_SEATS - NR;
+    // the lean instantiation exists for the default block size of the shape only
+    constexpr bool lean = NF_ALL > 1 && MC_THREADS == (NR <= 3 ? 1024 : 768);
+    if constexpr (lean) { if (prm.n_fixed <= 1) return launch_mc_nfx<NR, MC_THREADS, 1>(prm, tb, d_counts, grid, st); }
+    return launch_mc_nfx<NR, MC_THREADS, NF_ALL>(prm, tb, d_counts, grid, st);
 }
 
 cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
