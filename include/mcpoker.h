@@ -8,6 +8,7 @@
  *                        (5/6/7 cards = flop/turn/river), one hand
  *   mc_eval7_batch[_dev] the same, lifted over a batch (`(map #(player->hand-value board %) ids)`,
  *                        gameplay.clj:127-128)
+ *   mc_eval_batch_packed48  the same batch with hands as 6-byte fields of card positions (the compact wire format)
  *   mc_showdown          gameplay.clj:127-132 `end-game` ranking + :118-120 `group-winners`
  *   mc_enumerate7*       player->hand-value over every C(52,7) hand (BASELINE config 2)
  *   mc_equity_exhaustive* end-game ranking over every completion of the board (config 3)
