@@ -358,16 +358,9 @@ size_t stage_hands() {        // hands per pipeline stage of the host-buffer cal
 // host buffers -> keys.  The input is either masks (8 B per hand) or packed48 hands (6 B per hand, expanded to masks
 // on the device).  Contiguous slice per device, each streamed through N_SLOTS staging buffers on their own streams so
 // the H2D copy of stage i+1, the kernel(s) of stage i and the D2H copy of stage i-1 overlap.
-int eval_batch_host(const void *in, bool packed48, size_t n, uint32_t *keys, int key_format) {
-    int rc = need_init();
-    if (rc) return rc;
-    if (n == 0) return MC_OK;
-    if (!in || !keys) return fail(MC_ERR_INVALID, "null buffer");
-    const size_t in_bytes = packed48 ? 6 : sizeof(uint64_t);
-    const unsigned char *src = static_cast<const unsigned char *>(in);
+int eval_batch_pipeline(const unsigned char *src, size_t in_bytes, bool packed48, size_t n, uint32_t *keys, int key_format) {
+    int rc;
     const int nd = (int)g_ctx.size();
-    std::vector<std::unique_lock<std::mutex>> locks;
-    for (auto &c : g_ctx) locks.emplace_back(c->mu);
     const size_t per_dev = (n + nd - 1) / nd;
     std::vector<size_t> pos(nd), end(nd);
     for (int d = 0; d < nd; d++) {
@@ -407,6 +400,25 @@ int eval_batch_host(const void *in, bool packed48, size_t n, uint32_t *keys, int
         for (int s = 0; s < N_SLOTS; s++) CU(cudaStreamSynchronize(c.slot_stream[s]));
     }
     return MC_OK;
+}
+int eval_batch_host(const void *in, bool packed48, size_t n, uint32_t *keys, int key_format) {
+    int rc = need_init();
+    if (rc) return rc;
+    if (n == 0) return MC_OK;
+    if (!in || !keys) return fail(MC_ERR_INVALID, "null buffer");
+    const size_t in_bytes = packed48 ? 6 : sizeof(uint64_t);
+    const unsigned char *src = static_cast<const unsigned char *>(in);
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    rc = eval_batch_pipeline(src, in_bytes, packed48, n, keys, key_format);
+    if (rc) {
+        // a failed call must not leave copies into the caller's buffers in flight: drain the stage streams
+        for (auto &c : g_ctx)
+            if (c->d_in[0] && cudaSetDevice(c->device) == cudaSuccess)
+                for (int s = 0; s < N_SLOTS; s++) (void)cudaStreamSynchronize(c->slot_stream[s]);
+        (void)cudaGetLastError();
+    }
+    return rc;
 }
 }  // namespace
 
