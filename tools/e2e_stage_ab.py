@@ -11,9 +11,9 @@ import mcb200_loader  # noqa: E402
 pkg = mcb200_loader.load()
 E = pkg.engine
 torch.cuda.set_device(0)
-E.init(devices=[0])
+ndev = E.init() if os.environ.get("MCP_ALL_DEVICES") else E.init(devices=[0])      # all devices in ONE process: the JVM-host mode
 L = E.lib()
-n = 1 << 26
+n = 1 << int(os.environ.get("MCP_E2E_LOG2", "26"))
 st = torch.cuda.current_stream().cuda_stream
 d = torch.empty(n, dtype=torch.int64, device="cuda")
 E.check(L.mc_random_hands_dev(0x5EED5EED, 0, n, 7, d.data_ptr(), st))
@@ -39,5 +39,5 @@ for name, fn in (("mask", lambda: E.check(L.mc_eval7_batch(h_masks.data_ptr(), n
         fn()
         best = min(best, time.perf_counter() - t0)
     res[name] = n / best / 1e9
-print("stage 2^%s: mask %.2f G evals/s, packed48 %.2f G evals/s, equal %s" % (
-    os.environ.get("MCP_STAGE_LOG2", "22"), res["mask"], res["packed48"], torch.equal(k1, k2)))
+print("%d device(s) in one process, 2^%d hands, stage 2^%s: mask %.2f G evals/s, packed48 %.2f G evals/s, equal %s" % (
+    ndev, n.bit_length() - 1, os.environ.get("MCP_STAGE_LOG2", "22"), res["mask"], res["packed48"], torch.equal(k1, k2)))
