@@ -82,17 +82,24 @@
 (defn four-of-a-kind? [cards] (n-of-a-kind? cards 4))
 (defn three-of-a-kind? [cards] (n-of-a-kind? cards 3))
 (defn pair? [cards] (n-of-a-kind? cards 2))
+;; n-pairs? :71-79.  The reference walks the 120 (or 24, ...) index-lexicographic permutations of the cards and keeps
+;; the first whose leading k1 cards and following k2 cards are each of one rank.  `take` past the end of the
+;; permutation gives a SHORT (or empty) group, and a group of fewer than two cards is rank-constant, so four 2s are
+;; a "full house" (test :36: trips + the one card left) and a "two pair" (:49).  Same search here, so the same first
+;; hit and the same truthiness for every input; only the values of `evaluator` go to the GPU.
+(defn- orderings [v]                      ; index-lexicographic permutations of a vector
+  (if (empty? v)
+    [()]
+    (for [i (range (count v))
+          tail (orderings (into (subvec v 0 i) (subvec v (inc i))))]
+      (cons (v i) tail))))
 (defn n-pairs? [cards k1 k2]
-  (let [by-rank (vals (group-by :rank cards))
-        pick (fn [k skip] (first (filter #(and (>= (count %) k) (not= % skip)) (sort-by (comp - :rank first) by-rank))))]
-    ;; any split of the cards into a rank-constant k1-group and a rank-constant k2-group (k2 may reuse the rank
-    ;; of the k1-group when four of a kind are present, as the reference's permutation search does)
-    (some (fn [g1]
-            (some (fn [g2]
-                    (let [a (take k1 g1) b (take k2 (remove (set a) g2))]
-                      (when (and (= k1 (count a)) (= k2 (count b))) [a b])))
-                  by-rank))
-          by-rank)))
+  (let [one-rank? #(constant-cards? % :rank)]
+    (first (for [o (orderings (vec cards))
+                 :let [g1 (sort-by :rank (take k1 o))
+                       g2 (sort-by :rank (take k2 (drop k1 o)))]
+                 :when (and (one-rank? g1) (one-rank? g2))]
+             [g1 g2]))))
 (defn full-house? [cards] (n-pairs? cards 3 2))
 (defn two-pair? [cards] (n-pairs? cards 2 2))
 (defn cards->ranks [cards] (reverse (sort (map :rank cards))))

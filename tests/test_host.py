@@ -126,6 +126,38 @@ def test_mirror_predicates_like_the_reference_tests(pkg):
     assert he.max_hand_value([6, [8, 8, 8, 9, 9], []], [6, [9, 9, 9, 8, 8], []]) == [6, [9, 9, 9, 8, 8], []]
 
 
+def test_mirror_predicate_trace_table(pkg):
+    """every predicate assert of hand_evaluator_test.clj:6-55 (tests/golden/reference_vectors.json "predicates", the same
+    table INTEGRATION.md traces through the Clojure drop-in) against the Python mirror: the two mirrors implement
+    n-pairs? by the same permutation search, so they cannot disagree on an assert without this test failing"""
+    import json
+    import random
+    he, card = pkg.hand_evaluator, pkg.card
+    table = json.load(open(os.path.join(ROOT, "tests", "golden", "reference_vectors.json")))["predicates"]["asserts"]
+    assert len(table) == 22
+    fns = {"constant-coll?": lambda e, cs: he.constant_coll_p(e["coll"]), "straight?": lambda e, cs: he.straight_p(cs),
+           "n-of-a-kind?": lambda e, cs: he.n_of_a_kind_p(cs, e["n"]), "full-house?": lambda e, cs: he.full_house_p(cs),
+           "two-pair?": lambda e, cs: he.two_pair_p(cs)}
+    for e in table:
+        cs = [card.COMPLETE_DECK[13 * s + r - 2] for s, r in e.get("cards", [])]
+        orders = [cs]
+        if e.get("shuffle"):
+            rng = random.Random(e["line"])
+            for _ in range(10):
+                c2 = cs[:]
+                rng.shuffle(c2)
+                orders.append(c2)
+        for o in orders:
+            got = fns[e["fn"]](e, o)
+            assert (got is not None) == e["truthy"], (e["line"], e["fn"])
+    # the shape n-pairs? returns where the reference's own test relies on a SHORT second group (:36, :49)
+    twos = [c for c in card.COMPLETE_DECK if c.rank == 2]
+    g1, g2 = he.full_house_p(twos)
+    assert len(g1) == 3 and len(g2) == 1
+    g1, g2 = he.two_pair_p(twos)
+    assert len(g1) == 2 and len(g2) == 2
+
+
 def test_pack_resuits_repeated_cards(pkg):
     he, card = pkg.hand_evaluator, pkg.card
     C_ = card.Card

@@ -62,6 +62,20 @@ def test_two_pair_p(oracle):                    # :44-55
     assert f(TWOS[:2] + THREES[:2] + FOURS[:1])
 
 
+def test_predicate_trace_table(oracle):         # :6-55, the table INTEGRATION.md traces through the Clojure drop-in
+    L = oracle.lib()
+    fns = {"constant-coll?": lambda e, cs: L.orc_constant_coll((C.c_int * len(e["coll"]))(*e["coll"]), len(e["coll"])),
+           "straight?": lambda e, cs: L.orc_straight_p(oracle.cards(cs), len(cs)),
+           "n-of-a-kind?": lambda e, cs: L.orc_n_of_a_kind_p(oracle.cards(cs), len(cs), e["n"], None),
+           "full-house?": lambda e, cs: L.orc_full_house_p(oracle.cards(cs), len(cs)),
+           "two-pair?": lambda e, cs: L.orc_two_pair_p(oracle.cards(cs), len(cs))}
+    table = GOLD["predicates"]["asserts"]
+    assert len(table) == 22
+    for e in table:
+        cs = [tuple(c) for c in e.get("cards", [])]
+        assert bool(fns[e["fn"]](e, cs)) == e["truthy"], (e["line"], e["fn"])
+
+
 @pytest.mark.parametrize("vec", GOLD["evaluator"], ids=lambda v: "line%d" % v["line"])
 def test_evaluator_reference_vectors(oracle, vec):      # :57-137, all 13 asserts
     cards = [tuple(c) for c in vec["cards"]]
