@@ -152,6 +152,29 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def packed48_dev(torch, masks):
+    """int64 card masks on the device -> the 6-byte wire format of mc_eval_batch_packed48 (uint8, 6 per hand)"""
+    m, h = masks.clone(), torch.zeros_like(masks)
+    for k in range(7):
+        low = m & -m
+        h |= (torch.log2(low.double()) + 0.5).long() << (6 * k)      # (+0.5: log2 of a power of two, rounded)
+        m &= m - 1
+    return h.view(torch.uint8).reshape(-1, 8)[:, :6].reshape(-1)
+
+
+def colex_ranks_dev(torch, masks):
+    """int64 masks of 7-card hands on the device -> int32 colex ranks over card ids (mc_eval_batch_colex32's input)"""
+    from math import comb
+    binom = torch.tensor([[comb(x, k) for x in range(52)] for k in range(8)], dtype=torch.int64, device=masks.device)
+    m, rank = masks.clone(), torch.zeros_like(masks)
+    for k in range(1, 8):
+        low = m & -m
+        pos = (torch.log2(low.double()) + 0.5).long()
+        rank += binom[k][13 * (pos >> 4) + (pos & 15) - 2]
+        m &= m - 1
+    return rank.to(torch.int32)
+
+
 def timed_region(torch, dist, world, fn, steps, warmup):
     """W untimed + K timed calls of fn(), CUDA events on the current stream, barrier + synchronize on both
     sides, max over ranks.  returns total milliseconds of the K steps."""
@@ -262,41 +285,48 @@ def run_ours(args):
         v_ms = timed_region(torch, dist, world, lambda: k1_step(fmt), max(2, args.steps // 2), 1)
         variants[name] = world * n * max(2, args.steps // 2) / (v_ms * 1e-3)
 
-    # ---- e2e: the host-buffer C-ABI call, pinned memory, H2D + kernel + D2H inside the timed region ----
+    # ---- e2e: the host-buffer C-ABI calls, pinned memory, H2D + kernels + D2H inside the timed region ----
+    # Three wire formats of the same batch call, all bound by the host link:
+    #   colex32   4 B in (colex rank of the 7 cards) + 2 B out (class id)      mc_eval_batch_colex32   <- the headline e2e
+    #   packed48  6 B in (seven 6-bit card positions) + 4 B out (nibble key)   mc_eval_batch_packed48
+    #   mask      8 B in (card mask) + 4 B out                                 mc_eval7_batch
+    # The compact inputs are produced on the device here (bit shuffling only) and land in pinned host memory before the
+    # timing; the run fails unless all three calls return the same values.
     ne = 1 << args.e2e_log2
     h_masks = torch.empty(ne, dtype=torch.int64).pin_memory()
     h_keys = torch.empty(ne, dtype=torch.int32).pin_memory()
     h_masks.copy_(masks[:ne])
+    h_pk = torch.empty(6 * ne, dtype=torch.uint8).pin_memory()
+    h_pk.copy_(packed48_dev(torch, masks[:ne]))
+    h_keys48 = torch.empty(ne, dtype=torch.int32).pin_memory()
+    h_ranks = torch.empty(ne, dtype=torch.int32).pin_memory()
+    h_ranks.copy_(colex_ranks_dev(torch, masks[:ne]))
+    h_cls = torch.empty(ne, dtype=torch.int16).pin_memory()
     torch.cuda.synchronize()
+    e2e_steps = max(2, args.steps // 2)
 
     def e2e_step():
         E.check(L.mc_eval7_batch(h_masks.data_ptr(), ne, h_keys.data_ptr()))
 
-    e2e_steps = max(2, args.steps // 2)
+    def e2e48_step():
+        E.check(L.mc_eval_batch_packed48(h_pk.data_ptr(), ne, h_keys48.data_ptr()))
+
+    def e2e32_step():
+        E.check(L.mc_eval_batch_colex32(h_ranks.data_ptr(), ne, h_cls.data_ptr()))
+
     e2e_ms = wall_region(torch, dist, world, e2e_step, e2e_steps, 1)
     e2e_value = world * ne * e2e_steps / (e2e_ms * 1e-3)
     if rank == 0 and not torch.equal(h_keys[:check_n], keys[:check_n].cpu()):
         raise SystemExit("e2e keys differ from the device-resident run")
-    # the compact wire format of the same call: 6 B per hand (seven 6-bit card positions) instead of an 8 B mask.
-    # The hands are packed on the device here (bit shuffling only) and land in pinned host memory before the timing.
-    m_dev, h_dev = masks[:ne].clone(), torch.zeros(ne, dtype=torch.int64, device="cuda")
-    for k in range(7):
-        low = m_dev & -m_dev
-        h_dev |= (torch.log2(low.double()) + 0.5).long() << (6 * k)      # (+0.5: log2 of a power of two, rounded)
-        m_dev &= m_dev - 1
-    h_pk = torch.empty(6 * ne, dtype=torch.uint8).pin_memory()
-    h_pk.copy_(h_dev.view(torch.uint8).reshape(-1, 8)[:, :6].reshape(-1))
-    h_keys48 = torch.empty(ne, dtype=torch.int32).pin_memory()
-    del m_dev, h_dev, low
-    torch.cuda.synchronize()
-
-    def e2e48_step():
-        E.check(L.mc_eval_batch_packed48(h_pk.data_ptr(), ne, h_keys48.data_ptr()))
-
     e2e48_ms = wall_region(torch, dist, world, e2e48_step, e2e_steps, 1)
     e2e48_value = world * ne * e2e_steps / (e2e48_ms * 1e-3)
     if not torch.equal(h_keys48, h_keys):
         raise SystemExit("packed48 keys differ from the mask call")
+    e2e32_ms = wall_region(torch, dist, world, e2e32_step, e2e_steps, 2)
+    e2e32_value = world * ne * e2e_steps / (e2e32_ms * 1e-3)
+    class_keys = torch.from_numpy(api.class_keys().astype(np.int64)).to(torch.int32)
+    if not torch.equal(class_keys[h_cls.long() & 0xFFFF], h_keys):
+        raise SystemExit("colex32 class ids differ from the mask call's keys")
     # the same call on pageable buffers (what a caller gets without mc_alloc_host / pinning)
     pg_masks, pg_keys = h_masks.numpy().copy(), np.empty(ne, dtype=np.uint32)
     E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
@@ -304,23 +334,39 @@ def run_ours(args):
     E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
     pageable_value = ne / (time.perf_counter() - t0)
     del pg_masks, pg_keys
-    # the host link alone: the same pinned buffers copied with nothing else running (what bounds e2e)
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-    masks[:ne].copy_(h_masks, non_blocking=True)
-    torch.cuda.synchronize()
-    ev[0].record(); masks[:ne].copy_(h_masks, non_blocking=True); ev[1].record()
-    ev[2].record(); h_keys.copy_(keys[:ne], non_blocking=True); ev[3].record()
-    torch.cuda.synchronize()
-    h2d_alone = 8 * ne / (ev[0].elapsed_time(ev[1]) * 1e-3) / 1e9
-    d2h_alone = 4 * ne / (ev[2].elapsed_time(ev[3]) * 1e-3) / 1e9
-    link = {"h2d_alone_gbs": h2d_alone, "d2h_alone_gbs": d2h_alone, "h2d_in_e2e_gbs": 8 * e2e_value / world / 1e9,
-            "d2h_in_e2e_gbs": 4 * e2e_value / world / 1e9, "frac_of_h2d_alone": 8 * e2e_value / world / 1e9 / h2d_alone,
-            "packed48_h2d_gbs": 6 * e2e48_value / world / 1e9, "packed48_d2h_gbs": 4 * e2e48_value / world / 1e9,
-            "packed48_frac_of_h2d_alone": 6 * e2e48_value / world / 1e9 / h2d_alone,
-            "pageable_buffers_evals_per_s_per_gpu": pageable_value,
-            "note": "the mask call moves 12 B per hand over the host link (8 in, 4 out), the packed48 call 10 B (6 in, 4 out), "
-                    "both directions at once; both are bound by the H2D direction (h2d_in_e2e_gbs etc. are the mask call's)"}
-    del masks, keys
+    # The host link alone, measured as a ceiling for ALL ranks at once: every rank copies the same pinned buffers at
+    # the same time (barrier + synchronize on both sides, max over ranks), nothing else running: H2D alone, D2H alone,
+    # and both directions together at the byte ratio of the colex32 call (4 in : 2 out) on two streams.
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    d_ranks, d_cls = torch.empty(ne, dtype=torch.int32, device="cuda"), torch.empty(ne, dtype=torch.int16, device="cuda")
+
+    def copy_h2d():
+        with torch.cuda.stream(s_in):
+            d_ranks.copy_(h_ranks, non_blocking=True)
+
+    def copy_d2h():
+        with torch.cuda.stream(s_out):
+            h_cls.copy_(d_cls, non_blocking=True)
+
+    def copy_both():
+        copy_h2d()
+        copy_d2h()
+
+    reps = 4
+    h2d_gbs = world * 4 * ne * reps / (wall_region(torch, dist, world, copy_h2d, reps, 1) * 1e-3) / 1e9
+    d2h_gbs = world * 2 * ne * reps / (wall_region(torch, dist, world, copy_d2h, reps, 1) * 1e-3) / 1e9
+    both_ms = wall_region(torch, dist, world, copy_both, reps, 1)
+    both_evals = world * ne * reps / (both_ms * 1e-3)               # hands/s if the copies were all there is to do
+    link = {"all_ranks_at_once": True, "h2d_alone_gbs_total": h2d_gbs, "d2h_alone_gbs_total": d2h_gbs,
+            "h2d_while_d2h_gbs_total": 4 * both_evals / 1e9, "d2h_while_h2d_gbs_total": 2 * both_evals / 1e9,
+            "ceiling_evals_per_s": both_evals,
+            "ceiling_note": "bare cudaMemcpyAsync of the colex32 call's buffers (4 B in + 2 B out per hand, both directions at "
+                            "once, every rank at the same time, nothing else running): what the host link of this box allows",
+            "colex32_frac_of_ceiling": e2e32_value / both_evals,
+            "colex32_h2d_gbs_total": 4 * e2e32_value / 1e9, "colex32_d2h_gbs_total": 2 * e2e32_value / 1e9,
+            "packed48_h2d_gbs_total": 6 * e2e48_value / 1e9, "mask_h2d_gbs_total": 8 * e2e_value / 1e9,
+            "pageable_buffers_evals_per_s_per_gpu": pageable_value}
+    del masks, keys, d_ranks, d_cls
 
     # ---- integer pipes of this GPU, measured in this run: thread-ops per clock per SM ----------------
     pipes = None
@@ -441,10 +487,10 @@ def run_ours(args):
         holes_sd = (C.c_uint64 * 9)(*[api.mask_of_ids([6 + i, 29 + 2 * i]) for i in range(9)])
         keys_sd, grp_sd, ng_sd = (C.c_uint32 * 9)(), (C.c_int32 * 9)(), C.c_int32(0)
         for _ in range(20):
-            E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd)))
+            E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd), None))
         t0 = time.perf_counter()
         for _ in range(500):
-            E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd)))
+            E.check(L.mc_showdown_groups(board9, holes_sd, 9, keys_sd, grp_sd, C.byref(ng_sd), None))
         work["showdown_9_seats_host_call"] = {"latency_us": 1e6 * (time.perf_counter() - t0) / 500,
                                               "note": "end-game ranking + group-winners of one table (gameplay.clj:127-132) per call; "
                                                       "seats by kernel parameter, result written to mapped pinned host memory: one launch + one sync"}
@@ -542,11 +588,14 @@ def run_ours(args):
                          "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "eval7_stream_hash_kernel", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
                          "int_issue_frac": (value / world) * OPS["eval"] / int_peak, "ops_per_eval": OPS["eval"]},
-            "e2e": {"value": e2e48_value, "unit": "evals/s", "h2d_bytes_per_step": 6 * ne, "d2h_bytes_per_step": 4 * ne,
+            "e2e": {"value": e2e32_value, "unit": "evals/s", "h2d_bytes_per_step": 4 * ne, "d2h_bytes_per_step": 2 * ne,
                     "hands_per_step": ne,
-                    "call": "mc_eval_batch_packed48 (pinned host buffers, 6-byte hands, 3-stage copy / expand / K1 / copy pipeline)",
+                    "call": "mc_eval_batch_colex32 (pinned host buffers; 4-byte colex ranks in, 2-byte class ids out; 3-stage "
+                            "copy / unrank / K1 / copy pipeline); values checked equal to the mask call's keys in this run",
+                    "packed48_call": {"value": e2e48_value, "h2d_bytes_per_step": 6 * ne, "d2h_bytes_per_step": 4 * ne,
+                                      "call": "mc_eval_batch_packed48 (6-byte hands in, 4-byte nibble keys out)"},
                     "mask_call": {"value": e2e_value, "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,
-                                  "call": "mc_eval7_batch (8-byte masks, same pipeline without the expander)"},
+                                  "call": "mc_eval7_batch (8-byte masks in, 4-byte nibble keys out)"},
                     "link": link},
             "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
             "k1_variants_evals_per_s": variants, "int_pipes_measured": pipes, "workloads": work,

@@ -8,7 +8,10 @@
  *                        (5/6/7 cards = flop/turn/river), one hand
  *   mc_eval7_batch[_dev] the same, lifted over a batch (`(map #(player->hand-value board %) ids)`,
  *                        gameplay.clj:127-128)
- *   mc_eval_batch_packed48  the same batch with hands as 6-byte fields of card positions (the compact wire format)
+ *   mc_eval_batch_packed48  the same batch with hands as 6-byte fields of card positions (compact wire format)
+ *   mc_eval_batch_colex32   the same batch with 7-card hands as 4-byte colex ranks in, 2-byte class ids out (the most
+ *                        compact wire format: the host-buffer calls are bound by the host link)
+ *   mc_end_game          end-game in one call: ranking, tie groups, settlement of the pots (gameplay.clj:122-133)
  *   mc_showdown          gameplay.clj:127-132 `end-game` ranking + :118-120 `group-winners`
  *   mc_enumerate7*       player->hand-value over every C(52,7) hand (BASELINE config 2)
  *   mc_equity_exhaustive* end-game ranking over every completion of the board (config 3)
@@ -26,12 +29,18 @@
  *             Unsigned order of keys == clojure.core/compare order of the values; equal keys <=> `=` values.
  *             hit lengths by cat 0..8: 5,2,4,3,5,5,5,4,5.   0xFFFFFFFF marks an invalid input hand.
  *             MC_KEY_PACKED: cat<<28 | P<<14 | S with P, S 14-bit rank sets (bit r-1): same order, decodes
- *             to the same value (mc_key_packed_to_nibble); it is what the equity kernels compare internally.
+ *             to the same value (mc_key_packed_to_nibble).
+ *   class id  uint16, MC_KEY_CLASS16: the index of the value in the ascending list of all 7,462 distinct five-card
+ *             values (the best five of 6 or 7 cards is one of them; 4,892 occur for 7 cards).  Same order as the keys,
+ *             so class ids compare directly; mc_class_keys() hands out the list (class id -> nibble key, 30 KB) once.
+ *             0xFFFF marks an invalid input hand (and the reference tests' rank-1 hands, which have no class).
  *
  * Every function returns 0 (MC_OK) or a negative MC_ERR_*; mc_last_error() holds a thread-local message.
  * The caller owns every buffer it passes; the library owns device memory, streams and tables.  All entry
- * points are thread-safe (calls that touch the same device are serialised inside the library).  There is
- * no CPU fallback: without a usable sm_100 device every compute call fails with MC_ERR_NO_DEVICE.
+ * points are thread-safe (calls that touch the same device are serialised inside the library), and that includes
+ * the lifecycle: mc_init* / mc_shutdown wait for the calls in flight and no call starts on a context that is being
+ * torn down (a call that arrives after mc_shutdown fails with MC_ERR_NOT_INIT).  There is no CPU fallback: without a
+ * usable sm_100 device every compute call fails with MC_ERR_NO_DEVICE.
  */
 #ifndef MCPOKER_H
 #define MCPOKER_H
@@ -52,7 +61,16 @@ extern "C" {
 
 #define MC_KEY_NIBBLE       0
 #define MC_KEY_PACKED       1
+/* 2, 3, 4: A/B variants of the nibble-key kernels (bench.py) */
+#define MC_KEY_CLASS16      5   /* uint16 class ids instead of uint32 keys */
 #define MC_KEY_INVALID      0xFFFFFFFFu
+#define MC_CLASS_INVALID    0xFFFFu
+#define MC_N_HAND_CLASSES   7462
+
+/* input formats of mc_eval_batch */
+#define MC_IN_MASK64        0   /* uint64 card masks, 8 B per hand (5..7 cards) */
+#define MC_IN_PACKED48      1   /* seven 6-bit card positions, 6 B per hand (5..7 cards) */
+#define MC_IN_COLEX32       2   /* uint32 colex rank of a 7-card hand over card ids, 4 B per hand */
 
 #define MC_MAX_SEATS        9
 #define MC_N_CLASSES        169
@@ -81,6 +99,16 @@ int  mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key
  * is 4/3 of the throughput.  A repeated card or a malformed field gives MC_KEY_INVALID for that hand.  Replaces the
  * same reference lines as mc_eval7_batch (hand_evaluator.clj:162-172 over a batch). */
 int  mc_eval_batch_packed48(const uint8_t *hands /* 6*n bytes */, size_t n, uint32_t *keys);
+/* The most compact wire format: a 7-card hand as the colex rank of its card ids, sum_i C(c_i, i+1) with c_0 < ... < c_6
+ * (the combination index of mc_enumerate7_range; < C(52,7) = 133,784,560 < 2^27) in, its class id out: 4 B + 2 B per hand
+ * over the host link instead of 8 + 4.  A rank >= C(52,7) gives MC_CLASS_INVALID.  Unranked on the device. */
+int  mc_eval_batch_colex32(const uint32_t *ranks, size_t n, uint16_t *classes);
+/* Every combination of the above: in_format MC_IN_*, key_format MC_KEY_* (out = uint32 keys, or uint16 class ids for
+ * MC_KEY_CLASS16).  stage_cards: 5, 6 or 7 = the batch is flop / turn / river hands, 0 = decide from the first hand; it
+ * only selects the kernel's table image -- hands of another size are still evaluated exactly, just slower. */
+int  mc_eval_batch(const void *hands, int in_format, size_t n, void *out, int key_format, int stage_cards);
+/* class id -> nibble key, MC_N_HAND_CLASSES entries, ascending (so class ids order like keys).  Needs mc_init. */
+int  mc_class_keys(uint32_t *keys, int n /* = MC_N_HAND_CLASSES */);
 /* Page-locked host memory for the buffers of the host-buffer calls: they copy straight from / into the caller's
  * memory, which runs at the full host-link rate only when it is pinned (a JVM caller wraps the pointer in a direct
  * ByteBuffer).  Pageable buffers are accepted everywhere, just slower.  Needs mc_init. */
@@ -88,11 +116,14 @@ void *mc_alloc_host(size_t bytes);                                              
 int  mc_free_host(void *p);
 int  mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void *stream);
 int  mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream);
+/* device buffers, any key format (d_out: uint32 keys or uint16 class ids) and stage (5, 6: flop / turn image; else river) */
+int  mc_eval_batch_dev(const uint64_t *d_masks, size_t n, void *d_out, int key_format, int stage_cards, void *stream);
+int  mc_unrank_colex32_dev(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, void *stream);   /* colex ranks -> masks */
 int  mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
                  uint32_t *keys, uint32_t *winner_bitmask);
 /* full end-game grouping: group_of[seat] = index of its tie group, 0 = best (gameplay.clj:118-120) */
 int  mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
-                        uint32_t *keys, int32_t *group_of, int32_t *n_groups);
+                        uint32_t *keys, int32_t *group_of, int32_t *n_groups, uint32_t *winner_bitmask /* nullable */);
 
 /* pot settlement of end-game: update-stacks gameplay.clj:104-116 over the Bet records of bet.clj:7-8.  Pure integer
  * host arithmetic (no evaluation): for every pot, the FIRST tie group (group_of ascending = best first) that holds one
@@ -102,6 +133,11 @@ int  mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_s
  * divides by zero there). */
 int  mc_settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
                     const uint32_t *pot_players, int n_pots, int64_t *delta);
+/* end-game (gameplay.clj:122-133) in one call: mc_showdown_groups followed by mc_settle_pots on its groups.  keys,
+ * group_of, n_groups, winner_bitmask are nullable; delta[seat] is accumulated into. */
+int  mc_end_game(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
+                 const uint32_t *pot_players, int n_pots, uint32_t *keys, int32_t *group_of, int32_t *n_groups,
+                 uint32_t *winner_bitmask, int64_t *delta);
 
 /* ---- synthetic inputs (BASELINE config 1: Philox-seeded random hands, identical on CPU and GPU) --- */
 int  mc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *masks);

@@ -86,6 +86,62 @@ def eval_batch_packed48(packed, out=None):
     return keys
 
 
+def colex_rank(masks):
+    """uint64 masks of 7-card hands of the deck -> uint32 colex ranks over card ids (sum_i C(c_i, i+1)); host
+    arithmetic in numpy: what a caller of mc_eval_batch_colex32 computes from its cards"""
+    from math import comb
+    m = np.ascontiguousarray(masks, dtype=np.uint64).copy()
+    binom = np.array([[comb(x, k) for x in range(52)] for k in range(8)], dtype=np.uint64)
+    rank = np.zeros(m.shape[0], dtype=np.uint64)
+    one = np.uint64(1)
+    for k in range(1, 8):
+        low = m & (~m + one)
+        pos = np.zeros(m.shape[0], dtype=np.int64)
+        for b in (32, 16, 8, 4, 2, 1):
+            big = (low >> np.uint64(b)) != 0
+            pos += np.where(big, b, 0)
+            low = np.where(big, low >> np.uint64(b), low)
+        if np.any(m == 0):
+            raise ValueError("a hand holds fewer than 7 cards")
+        cid = 13 * (pos >> 4) + (pos & 15) - 2
+        if np.any((cid < 0) | (cid > 51) | ((pos & 15) < 2) | ((pos & 15) > 14)):
+            raise ValueError("a bit that is not one of the 52 cards")
+        rank += binom[k][cid]
+        m &= m - one
+    if np.any(m):
+        raise ValueError("a hand holds more than 7 cards")
+    return rank.astype(np.uint32)
+
+
+def eval_batch_colex32(ranks, out=None):
+    """uint32 colex ranks of 7-card hands -> uint16 class ids (class_keys()[id] = nibble key)"""
+    E.ensure_init()
+    ranks = np.ascontiguousarray(ranks, dtype=np.uint32)
+    cls = out if out is not None else np.empty(ranks.shape[0], dtype=np.uint16)
+    E.check(E.lib().mc_eval_batch_colex32(ranks.ctypes.data, ranks.shape[0], cls.ctypes.data))
+    return cls
+
+
+def eval_batch(hands, in_format, key_format=E.KEY_NIBBLE, stage_cards=0):
+    """any wire format in (IN_MASK64 uint64, IN_PACKED48 6 bytes, IN_COLEX32 uint32), keys (uint32) or class ids
+    (uint16, KEY_CLASS16) out"""
+    E.ensure_init()
+    dt, per = {E.IN_MASK64: (np.uint64, 1), E.IN_PACKED48: (np.uint8, 6), E.IN_COLEX32: (np.uint32, 1)}[in_format]
+    hands = np.ascontiguousarray(hands, dtype=dt)
+    n = hands.size // per
+    out = np.empty(n, dtype=np.uint16 if key_format == E.KEY_CLASS16 else np.uint32)
+    E.check(E.lib().mc_eval_batch(hands.ctypes.data, in_format, n, out.ctypes.data, key_format, stage_cards))
+    return out
+
+
+def class_keys():
+    """class id -> nibble key (7,462 entries, ascending)"""
+    E.ensure_init()
+    out = np.empty(E.N_HAND_CLASSES, dtype=np.uint32)
+    E.check(E.lib().mc_class_keys(out.ctypes.data, E.N_HAND_CLASSES))
+    return out
+
+
 def random_hands(seed, first, n, n_cards=7):
     E.ensure_init()
     out = np.empty(n, dtype=np.uint64)
@@ -98,9 +154,30 @@ def showdown(board_mask, hole_masks):
     E.ensure_init()
     n = len(hole_masks)
     h = (C.c_uint64 * max(n, 1))(*hole_masks)
-    keys, groups, ng = (C.c_uint32 * 9)(), (C.c_int32 * 9)(), C.c_int32(0)
-    rc = E.check(E.lib().mc_showdown_groups(board_mask, h, n, keys, groups, C.byref(ng)))
-    return list(keys[:n]), rc, list(groups[:n]), ng.value
+    keys, groups, ng, win = (C.c_uint32 * 9)(), (C.c_int32 * 9)(), C.c_int32(0), C.c_uint32(0)
+    E.check(E.lib().mc_showdown_groups(board_mask, h, n, keys, groups, C.byref(ng), C.byref(win)))
+    return list(keys[:n]), win.value, list(groups[:n]), ng.value
+
+
+def _pot_arrays(pots):
+    k = len(pots)
+    bet = (C.c_int64 * max(k, 1))(*[p[0] for p in pots])
+    cnt = (C.c_int32 * max(k, 1))(*[p[1] for p in pots])
+    msk = (C.c_uint32 * max(k, 1))(*[sum(1 << s for s in p[2]) for p in pots])
+    return bet, cnt, msk, k
+
+
+def end_game(board_mask, hole_masks, pots):
+    """end-game in one call (gameplay.clj:122-133): pots = [(bet, n, [seats])] ->
+    (keys, winner bitmask, tie group per seat, number of groups, chips won per seat)"""
+    E.ensure_init()
+    n = len(hole_masks)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    keys, groups, ng, win = (C.c_uint32 * 9)(), (C.c_int32 * 9)(), C.c_int32(0), C.c_uint32(0)
+    bet, cnt, msk, k = _pot_arrays(pots)
+    delta = (C.c_int64 * 9)()
+    E.check(E.lib().mc_end_game(board_mask, h, n, bet, cnt, msk, k, keys, groups, C.byref(ng), C.byref(win), delta))
+    return list(keys[:n]), win.value, list(groups[:n]), ng.value, list(delta[:n])
 
 
 def settle_pots(group_of, pots):
@@ -108,10 +185,7 @@ def settle_pots(group_of, pots):
     pots = [(bet, n, [seats])] -> chips won per seat"""
     n = len(group_of)
     g = (C.c_int32 * n)(*group_of)
-    k = len(pots)
-    bet = (C.c_int64 * max(k, 1))(*[p[0] for p in pots])
-    cnt = (C.c_int32 * max(k, 1))(*[p[1] for p in pots])
-    msk = (C.c_uint32 * max(k, 1))(*[sum(1 << s for s in p[2]) for p in pots])
+    bet, cnt, msk, k = _pot_arrays(pots)
     delta = (C.c_int64 * n)()
     E.check(E.lib().mc_settle_pots(g, n, bet, cnt, msk, k, delta))
     return list(delta)

@@ -15,6 +15,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -47,7 +48,6 @@ struct DevCtx {
     unsigned long long *d_small = nullptr;        // SMALL_WORDS x u64 scratch
     unsigned long long *h_small = nullptr;        // pinned mirror (mapped)
     unsigned long long *hd_small = nullptr;       // the device's address of h_small
-    uint32_t ticket = 0;                          // sequence number of the single-call kernels (await_ticket)
     Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
     long long *d_wtl = nullptr;
     PfBoard *d_pb_boards = nullptr; size_t pb_board_cap = 0;            // config 5 by boards: board list, scratch, win matrix
@@ -77,8 +77,16 @@ struct DevCtx {
     }
 };
 
-std::mutex g_mu;
+// Lifetime of the device contexts.  Every entry point that touches g_ctx holds g_life SHARED for its whole duration
+// (struct Use below); mc_init* / mc_shutdown hold it EXCLUSIVE while they swap or destroy the contexts, so they wait for
+// the calls in flight and no call can start on a context that is being torn down.  Work on one device is serialised by
+// DevCtx::mu as before.  (An entry point takes the shared hold exactly once: nested public calls go through the
+// innermost function that takes it.)
+std::shared_mutex g_life;
 std::vector<std::unique_ptr<DevCtx>> g_ctx;
+std::atomic<uint32_t> g_ticket_seq{1};              // tickets of the single-call kernels: process-wide, never 0, so a
+                                                    // re-initialised context can never match a word left in pinned memory
+uint32_t next_ticket() { uint32_t t; do t = g_ticket_seq.fetch_add(1, std::memory_order_relaxed); while (t == 0); return t; }
 
 int make_info(int dev, DeviceInfo *out) {
     int major = 0, sms = 0;
@@ -92,22 +100,32 @@ int make_info(int dev, DeviceInfo *out) {
 // Hash tables of hashtab.cuh.  The representative hands are evaluated on the device with the bit-plane
 // evaluator (K1, packed keys); the host only lays the results out (hashtab_build.h).
 std::unique_ptr<HashTables> g_tables;
+std::unique_ptr<StreamImages> g_images;
+
+// packed keys of `masks` by the bit-plane kernel
+int eval_reps_on_device(DevCtx &c, const std::vector<uint64_t> &masks, std::vector<uint32_t> *packed) {
+    const size_t n = masks.size();
+    packed->resize(n);
+    uint64_t *d_m = nullptr; uint32_t *d_k = nullptr;
+    CU(cudaMalloc(&d_m, n * sizeof(uint64_t)));
+    cudaError_t e = cudaMalloc(&d_k, n * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_m, masks.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, c.stream);
+    if (e == cudaSuccess) e = launch_eval7_stream(d_m, n, d_k, K1_PACKED, c.info, c.stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(packed->data(), d_k, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+    cudaFree(d_m); cudaFree(d_k);
+    if (e != cudaSuccess) return cuda_fail(e, "evaluating the table representatives");
+    return MC_OK;
+}
 
 int build_tables(DevCtx &c) {
     std::vector<HashRep> reps;
     ht_representatives(HT_MUL_CANDIDATES[0], &reps);
-    const size_t n = reps.size();
-    std::vector<uint64_t> masks(n);
-    std::vector<uint32_t> packed(n);
-    for (size_t i = 0; i < n; i++) masks[i] = reps[i].mask;
-    uint64_t *d_m = nullptr; uint32_t *d_k = nullptr;
-    CU(cudaMalloc(&d_m, n * sizeof(uint64_t)));
-    CU(cudaMalloc(&d_k, n * sizeof(uint32_t)));
-    CU(cudaMemcpyAsync(d_m, masks.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, c.stream));
-    CU(launch_eval7_stream(d_m, n, d_k, K1_PACKED, c.info, c.stream));
-    CU(cudaMemcpyAsync(packed.data(), d_k, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.stream));
-    CU(cudaStreamSynchronize(c.stream));
-    cudaFree(d_m); cudaFree(d_k);
+    std::vector<uint64_t> masks(reps.size());
+    std::vector<uint32_t> packed;
+    for (size_t i = 0; i < reps.size(); i++) masks[i] = reps[i].mask;
+    int rc = eval_reps_on_device(c, masks, &packed);
+    if (rc) return rc;
     std::unique_ptr<HashTables> T(new HashTables());
     std::string err = "no multiplier tried";
     for (uint32_t mul : HT_MUL_CANDIDATES) {
@@ -116,29 +134,47 @@ int build_tables(DevCtx &c) {
         if (err.empty()) break;
     }
     if (!err.empty()) return fail(MC_ERR_CUDA, "hash table construction failed: " + err);
+    // the streaming kernel's images (river, flop / turn; key and class flavours) and the global class list
+    std::vector<StreamRep> sreps;
+    ht_stream_representatives(&sreps);
+    masks.resize(sreps.size());
+    for (size_t i = 0; i < sreps.size(); i++) masks[i] = sreps[i].mask;
+    rc = eval_reps_on_device(c, masks, &packed);
+    if (rc) return rc;
+    std::unique_ptr<StreamImages> I(new StreamImages());
+    err = ht_build_stream_images(sreps, packed, I.get());
+    if (!err.empty()) return fail(MC_ERR_CUDA, "stream image construction failed: " + err);
     g_tables = std::move(T);
+    g_images = std::move(I);
     return MC_OK;
 }
 
 int upload_tables(DevCtx &c) {
     const HashTables &T = *g_tables;
+    const StreamImages &I = *g_images;
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
     const size_t off_card = sizeof(HashBlob), off_nib = off_card + sizeof(T.card);
-    const size_t off_sb = (off_nib + T.nib_keys.size() * sizeof(uint32_t) + 255) & ~(size_t)255;
-    const size_t total = off_sb + SB_BYTES;
-    std::vector<unsigned char> sblob;
-    const std::string err = ht_build_stream_blob(T, &sblob, &c.tb.stream_hash);
-    if (!err.empty()) return fail(MC_ERR_CUDA, "stream blob construction failed: " + err);
+    const size_t off_cls = up(off_nib + T.nib_keys.size() * sizeof(uint32_t));
+    const size_t off_k7 = up(off_cls + I.class_nib.size() * sizeof(uint32_t)), off_c7 = off_k7 + up(Lay7::BYTES);
+    const size_t off_k56 = off_c7 + up(Lay7::BYTES), off_c56 = off_k56 + up(Lay56::BYTES);
+    const size_t total = off_c56 + up(Lay56::BYTES);
     CU(cudaMalloc(&c.d_tables, total));
     unsigned char *base = static_cast<unsigned char *>(c.d_tables);
     CU(cudaMemcpyAsync(base, &T.blob, sizeof(HashBlob), cudaMemcpyHostToDevice, c.stream));
     CU(cudaMemcpyAsync(base + off_card, T.card, sizeof(T.card), cudaMemcpyHostToDevice, c.stream));
     CU(cudaMemcpyAsync(base + off_nib, T.nib_keys.data(), T.nib_keys.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
-    CU(cudaMemcpyAsync(base + off_sb, sblob.data(), SB_BYTES, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_cls, I.class_nib.data(), I.class_nib.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_k7, I.key7.data(), Lay7::BYTES, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_c7, I.cls7.data(), Lay7::BYTES, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_k56, I.key56.data(), Lay56::BYTES, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpyAsync(base + off_c56, I.cls56.data(), Lay56::BYTES, cudaMemcpyHostToDevice, c.stream));
     CU(cudaStreamSynchronize(c.stream));
-    c.tb.d_stream_blob = base + off_sb;
     c.tb.d_blob = reinterpret_cast<const HashBlob *>(base);
     c.tb.d_card = reinterpret_cast<const CardKey *>(base + off_card);
     c.tb.d_nib = reinterpret_cast<const uint32_t *>(base + off_nib);
+    c.tb.d_class_nib = reinterpret_cast<const uint32_t *>(base + off_cls);
+    c.tb.img7 = StreamImage{base + off_k7, base + off_c7, I.h7};
+    c.tb.img56 = StreamImage{base + off_k56, base + off_c56, I.h56};
     c.tb.h_card = T.card;
     for (int i = 0; i < 10; i++) c.tb.cat_base.v[i] = T.cat_base[i];
     c.tb.n_classes = (uint32_t)T.nib_keys.size();
@@ -146,7 +182,7 @@ int upload_tables(DevCtx &c) {
 }
 
 int init_devices(const int *ids, int n) {
-    std::lock_guard<std::mutex> lk(g_mu);
+    std::unique_lock<std::shared_mutex> lk(g_life);          // waits for every call in flight
     int visible = 0;
     cudaError_t e = cudaGetDeviceCount(&visible);
     if (e != cudaSuccess || visible == 0) { cudaGetLastError(); return fail(MC_ERR_NO_DEVICE, "no CUDA device visible; libmcpoker has no CPU fallback"); }
@@ -154,7 +190,11 @@ int init_devices(const int *ids, int n) {
     if (ids) want.assign(ids, ids + n);
     else { if (n <= 0 || n > visible) n = visible; for (int i = 0; i < n; i++) want.push_back(i); }
     for (int d : want) if (d < 0 || d >= visible) return fail(MC_ERR_INVALID, "device id out of range");
-    g_ctx.clear();
+    for (size_t i = 0; i < want.size(); i++) for (size_t j = i + 1; j < want.size(); j++)
+        if (want[i] == want[j]) return fail(MC_ERR_INVALID, "a device id is listed twice");
+    // the new contexts are built aside and swapped in only when every device succeeded: a failure half way leaves the
+    // library exactly as it was
+    std::vector<std::unique_ptr<DevCtx>> fresh;
     for (int d : want) {
         std::unique_ptr<DevCtx> c(new DevCtx());
         int rc = make_info(d, &c->info);
@@ -164,19 +204,38 @@ int init_devices(const int *ids, int n) {
         CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
         CU(cudaMalloc(&c->d_small, SMALL_WORDS * sizeof(unsigned long long)));
         CU(cudaHostAlloc(&c->h_small, SMALL_WORDS * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
+        std::memset(c->h_small, 0, SMALL_WORDS * sizeof(unsigned long long));      // the ticket word must not hold a stale ticket
         CU(cudaHostGetDevicePointer(reinterpret_cast<void **>(&c->hd_small), c->h_small, 0));
         if (!g_tables) { rc = build_tables(*c); if (rc) return rc; }
         rc = upload_tables(*c);
         if (rc) return rc;
-        g_ctx.push_back(std::move(c));
+        fresh.push_back(std::move(c));
     }
+    g_ctx.swap(fresh);                                        // the old contexts are destroyed with `fresh`
     return MC_OK;
 }
 
-int need_init() {
-    if (g_ctx.empty()) return fail(MC_ERR_NOT_INIT, "mc_init has not been called");
-    return MC_OK;
-}
+// Shared hold on the device contexts for the duration of one entry point.
+struct Use {
+    std::shared_lock<std::shared_mutex> lk{g_life};
+    int rc;
+    Use() { rc = g_ctx.empty() ? fail(MC_ERR_NOT_INIT, "mc_init has not been called") : MC_OK; }
+};
+
+// If a call returns early (a CUDA error half way), no asynchronous copy into the caller's or the call's own host
+// buffers may stay in flight: drain the streams of every context on the way out.  Free when nothing is pending.
+struct DrainOnExit {
+    bool armed = true;
+    ~DrainOnExit() {
+        if (!armed) return;
+        for (auto &c : g_ctx)
+            if (cudaSetDevice(c->device) == cudaSuccess) {
+                (void)cudaStreamSynchronize(c->stream);
+                if (c->d_in[0]) for (int s = 0; s < N_SLOTS; s++) (void)cudaStreamSynchronize(c->slot_stream[s]);
+            }
+        (void)cudaGetLastError();
+    }
+};
 
 // Wait for a single-call kernel (launch_showdown / launch_eval_one writing into the mapped h_small): poll the ticket
 // word it writes last instead of paying the stream synchronisation; a kernel that never delivers (launch failure,
@@ -209,19 +268,21 @@ int current_tables(DeviceInfo *di, const DeviceTables **tb) {
 }
 
 // K1 dispatch.  key_format: 0 nibble (the plane-hash kernel for aligned buffers, else the rank-set-table kernel),
-// 1 packed, 2 nibble via FLO loops, 3 nibble via the rank-set table, 4 nibble via the hash tables (A/B variants)
-// the plane-hash kernel serves every aligned batch: measured (tools/k1_crossover.py) it wins at every size (6 us floor:
+// 1 packed, 2 nibble via FLO loops, 3 nibble via the rank-set table, 4 nibble via the plane hash (A/B variants),
+// 5 = MC_KEY_CLASS16 (uint16 global class ids; plane-hash kernel only).  stage_cards 5 / 6 selects the flop / turn image.
+// The plane-hash kernel serves every aligned batch: measured (tools/k1_crossover.py) it wins at every size (6 us floor:
 // 184 KB staged by TMA; the rank-set-table kernel computes its 64 KB table in every block, 12 us)
-cudaError_t launch_k1(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, const DeviceInfo &di,
+cudaError_t launch_k1(const uint64_t *d_masks, size_t n, void *d_out, int key_format, int stage_cards, const DeviceInfo &di,
                       const DeviceTables *tb, cudaStream_t st) {
-    const bool aligned = ((reinterpret_cast<uintptr_t>(d_masks) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d_keys) & 7) == 0);
-    const bool can_hash = tb && tb->d_stream_blob && aligned;
-    if (key_format == 4 || (key_format == 0 && can_hash)) {
+    const bool cls = key_format == MC_KEY_CLASS16;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(d_masks) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d_out) & (cls ? 3 : 7)) == 0);
+    const bool can_hash = tb && tb->img7.d_key && aligned;
+    if (cls || key_format == 4 || (key_format == 0 && can_hash)) {
         if (!can_hash) return cudaErrorInvalidValue;
-        return launch_eval7_stream_hash(d_masks, n, d_keys, tb->d_stream_blob, tb->stream_hash, di, st);
+        return launch_eval_stream_hash(d_masks, n, d_out, cls, stage_cards, *tb, di, st);
     }
     const int mode = key_format == MC_KEY_PACKED ? K1_PACKED : (key_format == 2 ? K1_NIBBLE_FLO : K1_NIBBLE_TABLE);
-    return launch_eval7_stream(d_masks, n, d_keys, mode, di, st);
+    return launch_eval7_stream(d_masks, n, static_cast<uint32_t *>(d_out), mode, di, st);
 }
 
 int ensure_slots(DevCtx &c) {
@@ -272,11 +333,13 @@ int check_equity_args(const uint64_t *hole_masks, int n_seats, uint64_t board, u
 // run fn(ctx, lo, hi) on every device over an even split of [0, total), then sum `words` u64 of d_small
 template <typename F>
 int sharded_small_job(uint64_t total, int words, unsigned long long *sum, F launch) {
-    int rc = need_init();
-    if (rc) return rc;
+    Use use;
+    if (use.rc) return use.rc;
+    int rc;
     const int nd = (int)g_ctx.size();
     std::vector<std::unique_lock<std::mutex>> locks;
     for (auto &c : g_ctx) locks.emplace_back(c->mu);
+    DrainOnExit drain;
     const uint64_t per = (total + nd - 1) / nd;
     for (int d = 0; d < nd; d++) {
         DevCtx &c = *g_ctx[d];
@@ -300,7 +363,7 @@ int sharded_small_job(uint64_t total, int words, unsigned long long *sum, F laun
 
 extern "C" {
 
-int mc_abi_version(void) { return 1; }
+int mc_abi_version(void) { return 2; }
 const char *mc_last_error(void) { return g_err.c_str(); }
 
 int mc_init(int n_gpus, unsigned /*flags*/) { return init_devices(nullptr, n_gpus); }
@@ -309,11 +372,15 @@ int mc_init_devices(const int *device_ids, int n) {
     return init_devices(device_ids, n);
 }
 void mc_shutdown(void) {
-    std::lock_guard<std::mutex> lk(g_mu);
+    std::unique_lock<std::shared_mutex> lk(g_life);          // waits for every call in flight
     g_ctx.clear();
     g_tables.reset();
+    g_images.reset();
 }
-int mc_device_count(void) { return (int)g_ctx.size(); }
+int mc_device_count(void) {
+    std::shared_lock<std::shared_mutex> lk(g_life);
+    return (int)g_ctx.size();
+}
 
 uint64_t mc_card_bit(int card_id) {
     if (card_id < 0 || card_id >= 52) return 0;
@@ -334,16 +401,42 @@ int mc_key_decode(uint32_t key, int32_t *cat, int32_t hit[5], int32_t *n_hit, in
 }
 
 // ---- K1 --------------------------------------------------------------------------------------------
-int mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream) {
-    if (n && (!d_masks || !d_keys)) return fail(MC_ERR_INVALID, "null device buffer");
+namespace {
+bool key_format_ok(int f) { return f >= 0 && f <= MC_KEY_CLASS16; }
+}
+int mc_eval_batch_dev(const uint64_t *d_masks, size_t n, void *d_out, int key_format, int stage_cards, void *stream) {
+    if (n && (!d_masks || !d_out)) return fail(MC_ERR_INVALID, "null device buffer");
+    if (!key_format_ok(key_format)) return fail(MC_ERR_INVALID, "unknown key format");
+    std::shared_lock<std::shared_mutex> life(g_life);
     DeviceInfo di; const DeviceTables *tb = nullptr;
     int rc = current_info(&di, &tb);
     if (rc) return rc;
-    CU(launch_k1(d_masks, n, d_keys, key_format, di, tb, (cudaStream_t)stream));
+    if (key_format == MC_KEY_CLASS16 && !tb) return fail(MC_ERR_NOT_INIT, "mc_init / mc_init_devices has not been called for the current device");
+    CU(launch_k1(d_masks, n, d_out, key_format, stage_cards, di, tb, (cudaStream_t)stream));
     return MC_OK;
 }
+int mc_eval7_batch_dev_fmt(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int key_format, void *stream) {
+    if (key_format == MC_KEY_CLASS16) return fail(MC_ERR_INVALID, "class ids are 16-bit: use mc_eval_batch_dev");
+    return mc_eval_batch_dev(d_masks, n, d_keys, key_format, 7, stream);
+}
 int mc_eval7_batch_dev(const uint64_t *d_masks, size_t n, uint32_t *d_keys, void *stream) {
-    return mc_eval7_batch_dev_fmt(d_masks, n, d_keys, MC_KEY_NIBBLE, stream);
+    return mc_eval_batch_dev(d_masks, n, d_keys, MC_KEY_NIBBLE, 7, stream);
+}
+int mc_unrank_colex32_dev(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, void *stream) {
+    if (n && (!d_ranks || !d_masks)) return fail(MC_ERR_INVALID, "null device buffer");
+    std::shared_lock<std::shared_mutex> life(g_life);
+    DeviceInfo di;
+    int rc = current_info(&di);
+    if (rc) return rc;
+    CU(launch_unrank_colex32(d_ranks, n, d_masks, di, (cudaStream_t)stream));
+    return MC_OK;
+}
+int mc_class_keys(uint32_t *keys, int n) {
+    if (!keys || n != N_HAND_CLASSES) return fail(MC_ERR_INVALID, "keys must hold MC_N_HAND_CLASSES entries");
+    Use use;
+    if (use.rc) return use.rc;
+    std::memcpy(keys, g_images->class_nib.data(), (size_t)n * sizeof(uint32_t));
+    return MC_OK;
 }
 
 namespace {
@@ -355,20 +448,35 @@ size_t stage_hands() {        // hands per pipeline stage of the host-buffer cal
     }();
     return v;
 }
-// host buffers -> keys.  The input is either masks (8 B per hand) or packed48 hands (6 B per hand, expanded to masks
-// on the device).  Contiguous slice per device, each streamed through N_SLOTS staging buffers on their own streams so
-// the H2D copy of stage i+1, the kernel(s) of stage i and the D2H copy of stage i-1 overlap.
-int eval_batch_pipeline(const unsigned char *src, size_t in_bytes, bool packed48, size_t n, uint32_t *keys, int key_format) {
+size_t wire_bytes(int in_format) { return in_format == MC_IN_MASK64 ? 8 : in_format == MC_IN_PACKED48 ? 6 : 4; }
+// how many cards the FIRST hand of a host batch holds (the host-buffer calls pick the K1 image by it; hands of another
+// size are still evaluated exactly, on the kernel's slow path)
+int first_hand_cards(const unsigned char *src, int in_format) {
+    if (in_format == MC_IN_COLEX32) return 7;
+    uint64_t h = 0;
+    std::memcpy(&h, src, in_format == MC_IN_MASK64 ? 8 : 6);
+    if (in_format == MC_IN_MASK64) return __builtin_popcountll(h);
+    int n = 0;
+    for (int k = 0; k < 7; k++) n += ((h >> (6 * k)) & 63u) != 0;
+    return n;
+}
+// host buffers -> keys / classes.  The input is masks (8 B per hand), packed48 hands (6 B) or colex32 ranks (4 B), the
+// compact formats being expanded to masks on the device; the output nibble keys (4 B) or class ids (2 B).  Contiguous
+// slice per device, each streamed through N_SLOTS staging buffers on their own streams so that the H2D copy of stage
+// i+1, the kernel(s) of stage i and the D2H copy of stage i-1 overlap.
+int eval_batch_pipeline(const unsigned char *src, int in_format, size_t n, unsigned char *dst, int key_format, int stage_cards) {
     int rc;
     const int nd = (int)g_ctx.size();
-    const size_t per_dev = (n + nd - 1) / nd;
+    const size_t in_bytes = wire_bytes(in_format), out_bytes = key_format == MC_KEY_CLASS16 ? 2 : 4;
+    // slices start on even hands: the staging buffers keep the alignment of the two-hand loads / stores
+    const size_t per_dev = ((n + nd - 1) / nd + 1) & ~(size_t)1;
     std::vector<size_t> pos(nd), end(nd);
     for (int d = 0; d < nd; d++) {
         pos[d] = std::min(n, per_dev * d); end[d] = std::min(n, pos[d] + per_dev);
         if (end[d] > pos[d]) {
             CU(cudaSetDevice(g_ctx[d]->device));
             rc = ensure_slots(*g_ctx[d]);
-            if (!rc && packed48) rc = ensure_packed_slots(*g_ctx[d]);
+            if (!rc && in_format != MC_IN_MASK64) rc = ensure_packed_slots(*g_ctx[d]);
             if (rc) return rc;
         }
     }
@@ -381,14 +489,15 @@ int eval_batch_pipeline(const unsigned char *src, size_t in_bytes, bool packed48
             const int s = (int)(round % N_SLOTS);
             const size_t cnt = std::min(stage_hands(), end[d] - pos[d]);
             CU(cudaSetDevice(c.device));
-            if (packed48) {
-                CU(cudaMemcpyAsync(c.d_pk[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
-                CU(launch_unpack48(c.d_pk[s], cnt, c.d_in[s], c.info, c.slot_stream[s]));
-            } else {
+            if (in_format == MC_IN_MASK64) {
                 CU(cudaMemcpyAsync(c.d_in[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
+            } else {
+                CU(cudaMemcpyAsync(c.d_pk[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
+                if (in_format == MC_IN_PACKED48) CU(launch_unpack48(c.d_pk[s], cnt, c.d_in[s], c.info, c.slot_stream[s]));
+                else CU(launch_unrank_colex32(reinterpret_cast<const uint32_t *>(c.d_pk[s]), cnt, c.d_in[s], c.info, c.slot_stream[s]));
             }
-            CU(launch_k1(c.d_in[s], cnt, c.d_out[s], key_format, c.info, &c.tb, c.slot_stream[s]));
-            CU(cudaMemcpyAsync(keys + pos[d], c.d_out[s], cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.slot_stream[s]));
+            CU(launch_k1(c.d_in[s], cnt, c.d_out[s], key_format, stage_cards, c.info, &c.tb, c.slot_stream[s]));
+            CU(cudaMemcpyAsync(dst + pos[d] * out_bytes, c.d_out[s], cnt * out_bytes, cudaMemcpyDeviceToHost, c.slot_stream[s]));
             pos[d] += cnt;
             if (pos[d] < end[d]) more = true;
         }
@@ -401,35 +510,38 @@ int eval_batch_pipeline(const unsigned char *src, size_t in_bytes, bool packed48
     }
     return MC_OK;
 }
-int eval_batch_host(const void *in, bool packed48, size_t n, uint32_t *keys, int key_format) {
-    int rc = need_init();
-    if (rc) return rc;
+int eval_batch_host(const void *in, int in_format, size_t n, void *out, int key_format, int stage_cards) {
+    if (in_format < MC_IN_MASK64 || in_format > MC_IN_COLEX32) return fail(MC_ERR_INVALID, "unknown input format");
+    if (!key_format_ok(key_format)) return fail(MC_ERR_INVALID, "unknown key format");
+    Use use;
+    if (use.rc) return use.rc;
     if (n == 0) return MC_OK;
-    if (!in || !keys) return fail(MC_ERR_INVALID, "null buffer");
-    const size_t in_bytes = packed48 ? 6 : sizeof(uint64_t);
+    if (!in || !out) return fail(MC_ERR_INVALID, "null buffer");
     const unsigned char *src = static_cast<const unsigned char *>(in);
+    if (stage_cards == 0) stage_cards = first_hand_cards(src, in_format);
     std::vector<std::unique_lock<std::mutex>> locks;
     for (auto &c : g_ctx) locks.emplace_back(c->mu);
-    rc = eval_batch_pipeline(src, in_bytes, packed48, n, keys, key_format);
-    if (rc) {
-        // a failed call must not leave copies into the caller's buffers in flight: drain the stage streams
-        for (auto &c : g_ctx)
-            if (c->d_in[0] && cudaSetDevice(c->device) == cudaSuccess)
-                for (int s = 0; s < N_SLOTS; s++) (void)cudaStreamSynchronize(c->slot_stream[s]);
-        (void)cudaGetLastError();
-    }
-    return rc;
+    DrainOnExit drain;          // a failed call must not leave copies into the caller's buffers in flight
+    return eval_batch_pipeline(src, in_format, n, static_cast<unsigned char *>(out), key_format, stage_cards);
 }
 }  // namespace
 
+int mc_eval_batch(const void *hands, int in_format, size_t n, void *out, int key_format, int stage_cards) {
+    return eval_batch_host(hands, in_format, n, out, key_format, stage_cards);
+}
 int mc_eval7_batch_fmt(const uint64_t *masks, size_t n, uint32_t *keys, int key_format) {
-    return eval_batch_host(masks, false, n, keys, key_format);
+    if (key_format == MC_KEY_CLASS16) return fail(MC_ERR_INVALID, "class ids are 16-bit: use mc_eval_batch");
+    return eval_batch_host(masks, MC_IN_MASK64, n, keys, key_format, 0);
 }
 int mc_eval_batch_packed48(const uint8_t *hands, size_t n, uint32_t *keys) {
-    return eval_batch_host(hands, true, n, keys, MC_KEY_NIBBLE);
+    return eval_batch_host(hands, MC_IN_PACKED48, n, keys, MC_KEY_NIBBLE, 0);
+}
+int mc_eval_batch_colex32(const uint32_t *ranks, size_t n, uint16_t *classes) {
+    return eval_batch_host(ranks, MC_IN_COLEX32, n, classes, MC_KEY_CLASS16, 7);
 }
 void *mc_alloc_host(size_t bytes) {
-    if (need_init()) return nullptr;
+    Use use;
+    if (use.rc) return nullptr;
     void *p = nullptr;
     if (cudaSetDevice(g_ctx[0]->device) != cudaSuccess || cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
         fail(MC_ERR_CUDA, "cudaHostAlloc failed");
@@ -448,8 +560,9 @@ int mc_eval7_batch(const uint64_t *masks, size_t n, uint32_t *keys) {
 }
 
 int mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards, uint32_t *key) {
-    int rc = need_init();
-    if (rc) return rc;
+    Use use;
+    if (use.rc) return use.rc;
+    int rc;
     if (!suit_id || !rank || !key) return fail(MC_ERR_INVALID, "null argument");
     if (n_cards < 5) return fail(MC_ERR_TOO_FEW, "fewer than 5 cards: the reference raises ArityException here (hand_evaluator.clj:171-172)");
     if (n_cards > 7) return fail(MC_ERR_INVALID, "more than 7 cards");
@@ -466,7 +579,7 @@ int mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards, uint
     CU(cudaSetDevice(c.device));
     // the mask travels as a kernel parameter and the key is written straight into mapped pinned host memory:
     // one launch and one stream sync, no copies
-    const uint32_t ticket = ++c.ticket;
+    const uint32_t ticket = next_ticket();
     CU(launch_eval_one(m, reinterpret_cast<uint32_t *>(c.hd_small), ticket, c.stream));
     rc = await_ticket(c, ticket);
     if (rc) return rc;
@@ -474,35 +587,29 @@ int mc_eval_cards(const int32_t *suit_id, const int32_t *rank, int n_cards, uint
     return MC_OK;
 }
 
-int mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
-                       uint32_t *keys, int32_t *group_of, int32_t *n_groups) {
-    int rc = need_init();
-    if (rc) return rc;
+namespace {
+// one table through the showdown kernel: keys, tie groups, winner bitmask (the caller holds the shared hold)
+int showdown_locked(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, uint32_t *keys, int32_t *group_of,
+                    int32_t *n_groups, uint32_t *winner_bitmask) {
     EquityArgs a;
-    rc = check_equity_args(hole_masks, n_seats, board_mask, 0, false, &a, nullptr);
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, 0, false, &a, nullptr);
     if (rc) return rc;
     if (__builtin_popcountll(board_mask) < 3) return fail(MC_ERR_TOO_FEW, "fewer than 5 cards per player: the reference raises ArityException here");
     DevCtx &c = *g_ctx[0];
     std::lock_guard<std::mutex> lk(c.mu);
     CU(cudaSetDevice(c.device));
-    const uint32_t ticket = ++c.ticket;
+    const uint32_t ticket = next_ticket();
     CU(launch_showdown(a, reinterpret_cast<uint32_t *>(c.hd_small), ticket, c.stream));   // seats by parameter, result into mapped host memory
     rc = await_ticket(c, ticket);
     if (rc) return rc;
     const uint32_t *h = reinterpret_cast<const uint32_t *>(c.h_small);
     for (int s = 0; s < n_seats; s++) { if (keys) keys[s] = h[s]; if (group_of) group_of[s] = (int32_t)h[10 + s]; }
     if (n_groups) *n_groups = (int32_t)h[19];
-    return (int)h[9];       // winner bitmask (>= 0: at most 9 bits)
-}
-int mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, uint32_t *keys, uint32_t *winner_bitmask) {
-    const int rc = mc_showdown_groups(board_mask, hole_masks, n_seats, keys, nullptr, nullptr);
-    if (rc < 0) return rc;
-    if (winner_bitmask) *winner_bitmask = (uint32_t)rc;
+    if (winner_bitmask) *winner_bitmask = h[9];
     return MC_OK;
 }
-
-int mc_settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
-                   const uint32_t *pot_players, int n_pots, int64_t *delta) {
+int settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
+                const uint32_t *pot_players, int n_pots, int64_t *delta) {
     if (!group_of || !delta || n_seats < 1 || n_seats > MC_MAX_SEATS || n_pots < 0) return fail(MC_ERR_INVALID, "bad argument");
     if (n_pots && (!pot_bet || !pot_n || !pot_players)) return fail(MC_ERR_INVALID, "null pot array");
     for (int p = 0; p < n_pots; p++) {
@@ -517,11 +624,43 @@ int mc_settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet,
     }
     return MC_OK;
 }
+}  // namespace
+
+int mc_showdown_groups(uint64_t board_mask, const uint64_t *hole_masks, int n_seats,
+                       uint32_t *keys, int32_t *group_of, int32_t *n_groups, uint32_t *winner_bitmask) {
+    Use use;
+    if (use.rc) return use.rc;
+    return showdown_locked(board_mask, hole_masks, n_seats, keys, group_of, n_groups, winner_bitmask);
+}
+int mc_showdown(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, uint32_t *keys, uint32_t *winner_bitmask) {
+    Use use;
+    if (use.rc) return use.rc;
+    return showdown_locked(board_mask, hole_masks, n_seats, keys, nullptr, nullptr, winner_bitmask);
+}
+// end-game (gameplay.clj:122-133) in one call: ranking, tie groups and the settlement of the pots
+int mc_end_game(uint64_t board_mask, const uint64_t *hole_masks, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
+                const uint32_t *pot_players, int n_pots, uint32_t *keys, int32_t *group_of, int32_t *n_groups,
+                uint32_t *winner_bitmask, int64_t *delta) {
+    if (!delta) return fail(MC_ERR_INVALID, "delta is null");
+    Use use;
+    if (use.rc) return use.rc;
+    int32_t groups[MC_MAX_SEATS];
+    int rc = showdown_locked(board_mask, hole_masks, n_seats, keys, groups, n_groups, winner_bitmask);
+    if (rc) return rc;
+    if (group_of) for (int s = 0; s < n_seats; s++) group_of[s] = groups[s];
+    return settle_pots(groups, n_seats, pot_bet, pot_n, pot_players, n_pots, delta);
+}
+
+int mc_settle_pots(const int32_t *group_of, int n_seats, const int64_t *pot_bet, const int32_t *pot_n,
+                   const uint32_t *pot_players, int n_pots, int64_t *delta) {
+    return settle_pots(group_of, n_seats, pot_bet, pot_n, pot_players, n_pots, delta);
+}
 
 // ---- synthetic hands ------------------------------------------------------------------------------
 int mc_random_hands_dev(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks, void *stream) {
     if (n_cards < 1 || n_cards > 7) return fail(MC_ERR_INVALID, "n_cards must be 1..7");
     if (n && !d_masks) return fail(MC_ERR_INVALID, "null device buffer");
+    std::shared_lock<std::shared_mutex> life(g_life);
     DeviceInfo di;
     int rc = current_info(&di);
     if (rc) return rc;
@@ -529,8 +668,9 @@ int mc_random_hands_dev(uint64_t seed, uint64_t first, size_t n, int n_cards, ui
     return MC_OK;
 }
 int mc_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *masks) {
-    int rc = need_init();
-    if (rc) return rc;
+    Use use;
+    if (use.rc) return use.rc;
+    int rc;
     if (n_cards < 1 || n_cards > 7) return fail(MC_ERR_INVALID, "n_cards must be 1..7");
     if (n && !masks) return fail(MC_ERR_INVALID, "null buffer");
     DevCtx &c = *g_ctx[0];
@@ -552,6 +692,7 @@ int mc_enumerate7_dev(uint64_t first, uint64_t count, uint64_t *d_out, void *str
     const uint64_t total = host_binom(52, 7);
     if (first > total || count > total - first) return fail(MC_ERR_INVALID, "combination range out of bounds");
     if (!d_out) return fail(MC_ERR_INVALID, "null device buffer");
+    std::shared_lock<std::shared_mutex> life(g_life);
     DeviceInfo di; const DeviceTables *tb;
     int rc = current_tables(&di, &tb);
     if (rc) return rc;
@@ -588,6 +729,7 @@ int mc_equity_exhaustive_dev(const uint64_t *hole_masks, int n_seats, uint64_t b
     const uint64_t total = board_count(a);
     if (first_board > total || n_boards_in > total - first_board) return fail(MC_ERR_INVALID, "board range out of bounds");
     if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
+    std::shared_lock<std::shared_mutex> life(g_life);
     DeviceInfo di; const DeviceTables *tb;
     rc = current_tables(&di, &tb);
     if (rc) return rc;
@@ -631,6 +773,7 @@ int mc_equity_mc_dev(const uint64_t *hole_masks, int n_seats, uint64_t board_mas
     int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, true, &a, nullptr);
     if (rc) return rc;
     if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
+    std::shared_lock<std::shared_mutex> life(g_life);
     DeviceInfo di; const DeviceTables *tb;
     rc = current_tables(&di, &tb);
     if (rc) return rc;
@@ -714,8 +857,8 @@ void build_matchups_uncached(const std::vector<std::pair<int, int>> *only_cells,
     }
 }
 int run_matchups(const std::vector<Matchup> &mus, std::vector<long long> *wtl_full) {
-    int rc = need_init();
-    if (rc) return rc;
+    Use use;
+    if (use.rc) return use.rc;
     const int nd = (int)g_ctx.size();
     const size_t cells = (size_t)MC_N_CLASSES * MC_N_CLASSES * 3;
     std::vector<std::unique_lock<std::mutex>> locks;
@@ -724,6 +867,7 @@ int run_matchups(const std::vector<Matchup> &mus, std::vector<long long> *wtl_fu
     std::vector<std::vector<Matchup>> part(nd);
     for (size_t i = 0; i < mus.size(); i++) part[i % nd].push_back(mus[i]);
     std::vector<std::vector<long long>> host(nd, std::vector<long long>(cells));
+    DrainOnExit drain;                       // `host` must outlive every copy into it, also on an early error return
     for (int d = 0; d < nd; d++) {
         DevCtx &c = *g_ctx[d];
         CU(cudaSetDevice(c.device));
@@ -752,8 +896,8 @@ int run_matchups(const std::vector<Matchup> &mus, std::vector<long long> *wtl_fu
 
 int mc_equity_ranges(const int32_t *weight_a, const int32_t *weight_b, uint64_t board_mask, uint64_t dead_mask,
                      int64_t wtl[3], int64_t *total) {
-    int rc = need_init();
-    if (rc) return rc;
+    Use use;
+    if (use.rc) return use.rc;
     if (!weight_a || !weight_b || !wtl) return fail(MC_ERR_INVALID, "null argument");
     if ((board_mask & ~DECK_MASK) || (dead_mask & ~DECK_MASK) || (board_mask & dead_mask)) return fail(MC_ERR_INVALID, "bad board / dead mask");
     if (__builtin_popcountll(board_mask) > 5) return fail(MC_ERR_INVALID, "more than 5 community cards");
@@ -773,7 +917,14 @@ int mc_equity_ranges(const int32_t *weight_a, const int32_t *weight_b, uint64_t 
         mus.push_back(m);
     }
     if (52 - __builtin_popcountll(board_mask | dead_mask) - 4 < 5 - __builtin_popcountll(board_mask)) return fail(MC_ERR_INVALID, "not enough live cards");
+    {   // the weighted totals are int64: refuse ranges whose sum of weight products x boards cannot fit
+        const uint64_t boards = host_binom(52 - __builtin_popcountll(board_mask | dead_mask) - 4, 5 - __builtin_popcountll(board_mask));
+        unsigned __int128 tot = 0;
+        for (auto &m : mus) tot += (unsigned __int128)(uint64_t)m.weight * boards;
+        if (tot > (unsigned __int128)INT64_MAX) return fail(MC_ERR_INVALID, "sum of weight products x boards exceeds int64: scale the weights down");
+    }
     const int nd = (int)g_ctx.size();
+    DrainOnExit drain;
     std::vector<std::unique_lock<std::mutex>> locks;
     for (auto &c : g_ctx) locks.emplace_back(c->mu);
     const size_t per = (mus.size() + nd - 1) / nd;
@@ -883,8 +1034,8 @@ int mc_preflop_boards_count(int32_t *n_boards, int64_t *weight_sum) {
 
 int mc_preflop_wins_by_boards(int part, int n_parts, int64_t *win, int32_t *n_boards) {
     if (!win || n_parts < 1 || part < 0 || part >= n_parts) return fail(MC_ERR_INVALID, "bad part / n_parts");
-    int rc = need_init();
-    if (rc) return rc;
+    Use use;
+    if (use.rc) return use.rc;
     const std::vector<PfBoard> &all = canonical_boards();
     std::vector<PfBoard> mine;
     for (size_t i = (size_t)part; i < all.size(); i += (size_t)n_parts) mine.push_back(all[i]);
@@ -896,6 +1047,7 @@ int mc_preflop_wins_by_boards(int part, int n_parts, int64_t *win, int32_t *n_bo
     std::vector<std::vector<PfBoard>> share(nd);
     for (size_t i = 0; i < mine.size(); i++) share[i % nd].push_back(mine[i]);
     std::vector<std::vector<unsigned long long>> host(nd, std::vector<unsigned long long>(cells));
+    DrainOnExit drain;                       // `host` must outlive every copy into it, also on an early error return
     for (int d = 0; d < nd; d++) {
         DevCtx &c = *g_ctx[d];
         CU(cudaSetDevice(c.device));

@@ -71,12 +71,40 @@ MCP_HD uint32_t ht_class(uint32_t t, uint32_t sn, uint32_t mlo, uint32_t mhi,
 // [SB_V_OFF,   ...)     V', HT_SLOTS u16: byte address of the hand's nibble key
 // so a 7-card hand costs three data-dependent loads (D', V', key), plus the flush entry when one lane holds >= 5.
 struct StreamHash { uint32_t m1, m2, m3, m4; };
-constexpr uint32_t SB_KEY_OFF = 0;
-constexpr uint32_t SB_F_OFF = 20480;
-constexpr uint32_t SB_D_OFF = SB_F_OFF + HT_FLUSH * 2;
-constexpr uint32_t SB_V_OFF = SB_D_OFF + HT_BUCKETS * 2;
-constexpr uint32_t SB_BYTES = SB_V_OFF + HT_SLOTS * 2;
-static_assert(SB_BYTES % 16 == 0, "stream blob is copied in 16-byte units");
+// Two images with the same structure:
+//   Lay7   7-card hands (river): 49,205 rank multisets, 4,892 values; slot = (t >> 16) + D          184 KB
+//   Lay56  5- and 6-card hands (flop / turn, hand_evaluator.clj:171 on 5 or 6 cards): 6,175 + 18,395 multisets, up to
+//          7,462 values; slot = (t >> 17) + D                                                       ~130 KB
+// Each image exists twice on the device: "key" (the first region holds nibble keys) and "class" (the same region holds
+// the 16-bit global class id of the value: its index in the ascending list of all 7,462 five-card values,
+// mc_class_keys), so the last load of the kernel delivers whichever output format the call asked for.
+struct Lay7 {
+    static constexpr int N_MIN = 7, N_MAX = 7;                   // card counts the image serves
+    static constexpr uint32_t N_KEYS = 5120;                     // capacity of the first region (4,892 used)
+    static constexpr uint32_t SLOT_MUL = 65536u;                 // slot = umulhi(t, SLOT_MUL) + displacement
+    static constexpr uint32_t N_SLOTS = 65536u + 2048u;
+    static constexpr uint32_t KEY_OFF = 0;
+    static constexpr uint32_t F_OFF = KEY_OFF + 4u * N_KEYS;
+    static constexpr uint32_t D_OFF = F_OFF + HT_FLUSH * 2;
+    static constexpr uint32_t V_OFF = D_OFF + HT_BUCKETS * 2;
+    static constexpr uint32_t BYTES = V_OFF + N_SLOTS * 2;
+};
+struct Lay56 {
+    static constexpr int N_MIN = 5, N_MAX = 6;
+    static constexpr uint32_t N_KEYS = 7552;                     // 7,462 used
+    static constexpr uint32_t SLOT_MUL = 32768u;
+    static constexpr uint32_t N_SLOTS = 32768u + 2048u;
+    static constexpr uint32_t KEY_OFF = 0;
+    static constexpr uint32_t F_OFF = KEY_OFF + 4u * N_KEYS;
+    static constexpr uint32_t D_OFF = F_OFF + HT_FLUSH * 2;
+    static constexpr uint32_t V_OFF = D_OFF + HT_BUCKETS * 2;
+    static constexpr uint32_t BYTES = V_OFF + N_SLOTS * 2;
+};
+static_assert(Lay7::BYTES % 16 == 0 && Lay56::BYTES % 16 == 0, "stream images are copied in 16-byte units");
+static_assert(Lay7::V_OFF < 65536u && Lay56::V_OFF < 65536u, "key addresses are 16-bit");
+constexpr int N_HAND_CLASSES = 7462;                             // distinct five-card values
+constexpr uint32_t SB_KEY_OFF = Lay7::KEY_OFF, SB_F_OFF = Lay7::F_OFF, SB_D_OFF = Lay7::D_OFF, SB_V_OFF = Lay7::V_OFF;
+constexpr uint32_t SB_BYTES = Lay7::BYTES;
 MCP_HD uint32_t sb_key_addr(uint32_t dense) { return SB_KEY_OFF + 4u * dense; }
 MCP_HD uint32_t sb_flush_addr(uint32_t fi) { return SB_F_OFF + 2u * fi; }
 // rank-count bit planes of a card mask (carry-save addition of the four 16-bit suit lanes); low 16 bits valid
@@ -89,6 +117,7 @@ MCP_HD void sh_planes(uint32_t lo, uint32_t hi, uint32_t *c0, uint32_t *c1, uint
 MCP_HD uint32_t sh_t(uint32_t c0, uint32_t c1, uint32_t c2, const StreamHash &S) { return (c0 | c1 << 16) * S.m1 + c2 * S.m3; }
 MCP_HD uint32_t sh_b(uint32_t c0, uint32_t c1, uint32_t c2, const StreamHash &S) { return (c0 | c1 << 16) * S.m2 + c2 * S.m4; }
 MCP_HD uint32_t sh_bucket(uint32_t b) { return b >> 19; }
+template <class LAY> MCP_HD uint32_t sh_slot(uint32_t t) { return (uint32_t)(((uint64_t)t * LAY::SLOT_MUL) >> 32); }
 static_assert(HT_BUCKETS == 1 << 13, "sh_bucket takes the top 13 bits");
 
 }  // namespace mcp

@@ -10,6 +10,7 @@
 #include "eval_tbl.cuh"
 #include "hashtab.cuh"
 #include "philox.cuh"
+#include <type_traits>
 
 namespace mcp {
 
@@ -119,9 +120,11 @@ constexpr int K1H_THREADS = 1024;
 constexpr int K1H_RING_DEFAULT = 6;           // measured on a B200: 3: 482, 4: 508, 5: 515, 6: 532, 8: 525 G evals/s
 
 
-// The key of a 7-card hand of the 52-card deck; `odd` is non-zero for every other mask (bits outside the deck,
-// card count != 7), whose result is then meaningless but whose loads all stay inside the tables.
-// sb32 = shared address of the stream blob.
+// The value of a hand the image serves (LAY::N_MIN..N_MAX cards of the 52-card deck): its nibble key or, from the
+// class flavour of the image, its global class id.  `odd` is non-zero for every other mask (bits outside the deck,
+// another card count), whose result is then meaningless but whose loads all stay inside the tables.
+// sb32 = shared address of the stream image.
+template <class LAY>
 __device__ __forceinline__ uint32_t k1h_fast(uint64_t m, uint32_t sb32, const StreamHash &S, uint32_t &odd) {
     const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
     // per-rank card counts over the four suit lanes as bit planes: count = c0 + 2*c1 + 4*c2 (sh_planes)
@@ -144,36 +147,48 @@ __device__ __forceinline__ uint32_t k1h_fast(uint64_t m, uint32_t sb32, const St
     const bool low5 = pl >= 5;
     const uint32_t fm = low5 ? wl : __umulhi(wm, 65536u);
     const bool flush = low5 || (pw - pl >= 5);
-    odd = ((lo | hi) & 0x80038003u) | (uint32_t)(p01 + p23 - 7);
-    // D' holds 2 * displacement, so the byte address of the slot is one IMAD: 2 * (t >> 16) + D'[bucket]
-    const uint32_t d2 = lds_u16(sb32 + SB_D_OFF + __umulhi(b, 8192u) * 2u);
-    uint32_t ka = lds_u16(sb32 + SB_V_OFF + (__umulhi(t, 65536u) * 2u + d2));
-    if (flush) ka = lds_u16(sb32 + SB_F_OFF + (fm >> 1));      // == sb_flush_addr(fm >> 2)
+    if (LAY::N_MIN == LAY::N_MAX) odd = ((lo | hi) & 0x80038003u) | (uint32_t)(p01 + p23 - LAY::N_MIN);
+    else odd = ((lo | hi) & 0x80038003u) | (uint32_t)((uint32_t)(p01 + p23 - LAY::N_MIN) > (uint32_t)(LAY::N_MAX - LAY::N_MIN));
+    // D' holds 2 * displacement, so the byte address of the slot is one IMAD: 2 * slot + D'[bucket]
+    const uint32_t d2 = lds_u16(sb32 + LAY::D_OFF + __umulhi(b, 8192u) * 2u);
+    uint32_t ka = lds_u16(sb32 + LAY::V_OFF + (__umulhi(t, LAY::SLOT_MUL) * 2u + d2));
+    if (flush) ka = lds_u16(sb32 + LAY::F_OFF + (fm >> 1));    // F index = flush lane >> 2, two bytes each
     return lds_u32(sb32 + ka);
 }
 
-// everything that is not a 7-card hand of the 52-card deck
-__device__ __noinline__ uint32_t k1h_slow(uint64_t m) {
+// everything the image does not serve: other card counts, the tests' rank 1, invalid masks.  CLS: the global class id
+// (binary search of the nibble key in the ascending class list, global memory) instead of the key; 0xFFFF = invalid
+template <bool CLS>
+__device__ __noinline__ uint32_t k1h_slow(uint64_t m, const uint32_t *__restrict__ class_nib) {
     const uint32_t lo = (uint32_t)m, hi = (uint32_t)(m >> 32);
     const uint32_t n = (uint32_t)(__popc(lo) + __popc(hi));
     const bool ok = (((lo | hi) & 0x80018001u) == 0u) && (n - 5u <= 2u);
-    return ok ? packed_to_nibble(eval_packed(lo, hi)) : 0xFFFFFFFFu;
+    if (!ok) return CLS ? 0xFFFFu : 0xFFFFFFFFu;
+    const uint32_t key = packed_to_nibble(eval_packed(lo, hi));
+    if (!CLS) return key;
+    int a = 0, b = N_HAND_CLASSES - 1;                         // a rank-1 hand (test input only) has no class: 0xFFFF
+    while (a < b) { const int mid = (a + b) >> 1; if (class_nib[mid] < key) a = mid + 1; else b = mid; }
+    return class_nib[a] == key ? (uint32_t)a : 0xFFFFu;
 }
 
 // one launch covers at most 2^31 hands, so every index fits 32 bits (the launcher cuts longer batches)
-template <int K1H_RING>
+// OUT = uint32_t: nibble keys (key flavour of the image);  OUT = uint16_t: global class ids (class flavour)
+template <int K1H_RING, class LAY, typename OUT>
 __global__ void __launch_bounds__(K1H_THREADS, 1)
-eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restrict__ keys, uint32_t n,
-                         const uint4 *__restrict__ g_blob, const __grid_constant__ StreamHash S) {
+eval_stream_hash_kernel(const uint64_t *__restrict__ masks, OUT *__restrict__ keys, uint32_t n,
+                        const uint4 *__restrict__ g_blob, const __grid_constant__ StreamHash S,
+                        const uint32_t *__restrict__ class_nib) {
+    constexpr bool CLS = sizeof(OUT) == 2;
+    using OUT2 = typename std::conditional<CLS, uint32_t, uint2>::type;       // two results per store
     extern __shared__ __align__(16) unsigned char sb[];
     __shared__ unsigned long long mbar;
     BulkStage stage;
-    stage.start(&mbar, sb, g_blob, SB_BYTES);
+    stage.start(&mbar, sb, g_blob, LAY::BYTES);
     stage.wait();
     const uint32_t sb32 = staged_table_base(sb);
     const uint32_t npair = n >> 1;
     const ulonglong2 *in = reinterpret_cast<const ulonglong2 *>(masks);
-    uint2 *out = reinterpret_cast<uint2 *>(keys);
+    OUT2 *out = reinterpret_cast<OUT2 *>(keys);
     const uint32_t stride = gridDim.x * blockDim.x;
     // software pipeline: a thread evaluates two hands (16 bytes) per step and keeps the loads of its next RING - 1
     // steps in flight (80 B per thread, 80 KB per SM at RING = 6: HBM bandwidth x latency needs well over 32 KB
@@ -190,14 +205,14 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
             for (int k = 0; k < RING; k++) {
                 q[(k + RING - 1) % RING] = __ldcs(in + min(i + (RING - 1) * stride, last));
                 uint32_t o0, o1;
-                uint2 kk;
-                kk.x = k1h_fast(q[k].x, sb32, S, o0);
-                kk.y = k1h_fast(q[k].y, sb32, S, o1);
-                if (o0 | o1) {                                // never for 7-card hands of the deck: one divergent branch
-                    if (o0) kk.x = k1h_slow(q[k].x);
-                    if (o1) kk.y = k1h_slow(q[k].y);
+                uint32_t kx = k1h_fast<LAY>(q[k].x, sb32, S, o0);
+                uint32_t ky = k1h_fast<LAY>(q[k].y, sb32, S, o1);
+                if (o0 | o1) {                                // never for the hands the image serves: one divergent branch
+                    if (o0) kx = k1h_slow<CLS>(q[k].x, class_nib);
+                    if (o1) ky = k1h_slow<CLS>(q[k].y, class_nib);
                 }
-                __stcs(out + i, kk);
+                if constexpr (CLS) __stcs(out + i, kx | ky << 16);
+                else __stcs(out + i, make_uint2(kx, ky));
                 i += stride;
                 if (i >= npair) break;
             }
@@ -207,28 +222,40 @@ eval7_stream_hash_kernel(const uint64_t *__restrict__ masks, uint32_t *__restric
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
         const uint64_t m = masks[n - 1];
         uint32_t o;
-        const uint32_t k = k1h_fast(m, sb32, S, o);
-        keys[n - 1] = o ? k1h_slow(m) : k;
+        const uint32_t k = k1h_fast<LAY>(m, sb32, S, o);
+        keys[n - 1] = (OUT)(o ? k1h_slow<CLS>(m, class_nib) : k);
     }
 }
 
-cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
-                                     const StreamHash &S, const DeviceInfo &di, cudaStream_t st) {
-    if (n == 0) return cudaSuccess;
-    auto kern = eval7_stream_hash_kernel<K1H_RING_DEFAULT>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SB_BYTES);
+template <class LAY, typename OUT>
+static cudaError_t launch_stream_hash_t(const uint64_t *d_masks, size_t n, OUT *d_keys, const StreamImage &im,
+                                        const uint32_t *d_class_nib, const DeviceInfo &di, cudaStream_t st) {
+    auto kern = eval_stream_hash_kernel<K1H_RING_DEFAULT, LAY, OUT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LAY::BYTES);
     if (e != cudaSuccess) return e;
     constexpr size_t CHUNK = (size_t)1 << 30;                 // hands per launch: even, so every chunk keeps the alignment
     for (size_t off = 0; off < n; off += CHUNK) {
         const size_t m = n - off < CHUNK ? n - off : CHUNK;
         size_t want = (m + (size_t)K1H_THREADS * 4 - 1) / ((size_t)K1H_THREADS * 4);
         const int grid = (int)(want > (size_t)di.sm_count ? (size_t)di.sm_count : want);
-        kern<<<grid, K1H_THREADS, SB_BYTES, st>>>(d_masks + off, d_keys + off, (uint32_t)m,
-                                                  reinterpret_cast<const uint4 *>(d_stream_blob), S);
+        kern<<<grid, K1H_THREADS, LAY::BYTES, st>>>(d_masks + off, d_keys + off, (uint32_t)m,
+                                                    reinterpret_cast<const uint4 *>(sizeof(OUT) == 2 ? im.d_cls : im.d_key), im.hash, d_class_nib);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     return cudaSuccess;
+}
+
+cudaError_t launch_eval_stream_hash(const uint64_t *d_masks, size_t n, void *d_out, bool class16, int stage_cards,
+                                    const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const bool river = stage_cards != 5 && stage_cards != 6;
+    if (river) {
+        return class16 ? launch_stream_hash_t<Lay7>(d_masks, n, static_cast<uint16_t *>(d_out), tb.img7, tb.d_class_nib, di, st)
+                       : launch_stream_hash_t<Lay7>(d_masks, n, static_cast<uint32_t *>(d_out), tb.img7, tb.d_class_nib, di, st);
+    }
+    return class16 ? launch_stream_hash_t<Lay56>(d_masks, n, static_cast<uint16_t *>(d_out), tb.img56, tb.d_class_nib, di, st)
+                   : launch_stream_hash_t<Lay56>(d_masks, n, static_cast<uint32_t *>(d_out), tb.img56, tb.d_class_nib, di, st);
 }
 
 cudaError_t launch_eval7_stream(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int mode,
@@ -332,6 +359,49 @@ cudaError_t launch_unpack48(const unsigned char *d_packed, size_t n, uint64_t *d
     if (n == 0) return cudaSuccess;
     size_t want = (n / 4 + 255) / 256 + 1, cap = (size_t)di.sm_count * 8;
     unpack48_kernel<<<(int)(want > cap ? cap : want), 256, 0, st>>>(d_packed, n, d_masks);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// colex32 -> masks (mc_eval_batch_colex32): a 7-card hand travels as its colex rank over card ids, sum_i C(c_i, i+1)
+// < C(52,7) < 2^27 -- 4 B per hand over the host link instead of 8.  Unranking = seven branch-free binary searches
+// (six steps each) in a shared table of binomials padded with 0xFFFFFFFF: the largest x with C(x, k) <= rest is
+// automatically below the previous card, so no bound is carried.  A rank >= C(52,7) yields the mask 1 (not a card).
+// ---------------------------------------------------------------------------------------------------
+constexpr int UNR_COLS = 72;
+__global__ void __launch_bounds__(256)
+unrank_colex32_kernel(const uint32_t *__restrict__ ranks, size_t n, uint64_t *__restrict__ masks) {
+    __shared__ uint32_t sb[8 * UNR_COLS];                         // sb[k * 72 + x] = C(x, k) for x <= 52, else 2^32 - 1
+    for (int i = threadIdx.x; i < 8 * UNR_COLS; i += blockDim.x) {
+        const int k = i / UNR_COLS, x = i % UNR_COLS;
+        unsigned long long r = (k <= x) ? 1ull : 0ull;
+        for (int j = 1; j <= k && k <= x; j++) r = r * (unsigned long long)(x - k + j) / (unsigned long long)j;
+        sb[i] = x <= 52 ? (uint32_t)r : 0xFFFFFFFFu;
+    }
+    __syncthreads();
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint32_t rest = __ldcs(ranks + i);
+        uint64_t m = 1ull;
+        if (rest < cbinom(52, 7)) {
+            m = 0ull;
+#pragma unroll
+            for (int k = 7; k >= 1; k--) {
+                const uint32_t *row = sb + k * UNR_COLS;
+                uint32_t x = (uint32_t)k - 1u;                    // C(k-1, k) = 0 <= rest
+#pragma unroll
+                for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = x + step; if (row[y] <= rest) x = y; }
+                rest -= row[x];
+                m |= 1ull << id_to_pos((int)x);
+            }
+        }
+        masks[i] = m;
+    }
+}
+cudaError_t launch_unrank_colex32(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    size_t want = (n + 255) / 256, cap = (size_t)di.sm_count * 8;
+    unrank_colex32_kernel<<<(int)(want > cap ? cap : want), 256, 0, st>>>(d_ranks, n, d_masks);
     return cudaGetLastError();
 }
 

@@ -21,9 +21,16 @@ struct DeviceInfo { int sm_count; int device; };
 
 cudaError_t launch_eval7_stream(const uint64_t *d_masks, size_t n, uint32_t *d_keys, int mode,
                                 const DeviceInfo &di, cudaStream_t st);
-// requires 16-byte aligned masks / 8-byte aligned keys; d_stream_blob = SB_BYTES image (hashtab.cuh "K1 layout")
-cudaError_t launch_eval7_stream_hash(const uint64_t *d_masks, size_t n, uint32_t *d_keys, const void *d_stream_blob,
-                                     const StreamHash &S, const DeviceInfo &di, cudaStream_t st);
+struct DeviceTables;
+// K1, plane-hash kernel.  Requires 16-byte aligned masks and 8-byte (keys) / 4-byte (classes) aligned output.
+// class16: uint16 global class ids instead of uint32 nibble keys; stage_cards: 5 or 6 = the batch is flop / turn hands
+// (Lay56 image), anything else = river hands (Lay7 image); hands of another size than the image serves are still
+// evaluated correctly, on the slow path.
+cudaError_t launch_eval_stream_hash(const uint64_t *d_masks, size_t n, void *d_out, bool class16, int stage_cards,
+                                    const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+// colex ranks of 7-card hands over card ids (sum_i C(c_i, i+1), < C(52,7)) -> card masks; a rank out of range gives
+// the mask 1 (not a card), which every K1 variant maps to the invalid key / class
+cudaError_t launch_unrank_colex32(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,
                                 const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_unpack48(const unsigned char *d_packed, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st);
@@ -47,12 +54,13 @@ struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weig
 
 // ---- kernels on the additive-key / perfect-hash evaluator (kernels_hash.cu, hashtab.cuh) ----------------
 struct CatBase { uint32_t v[10]; };          // dense class index of the first class of each category; v[9] = #classes
+struct StreamImage { const void *d_key = nullptr, *d_cls = nullptr; StreamHash hash{}; };   // the two flavours of one layout
 struct DeviceTables {
     const HashBlob *d_blob = nullptr;        // device: D / F / V
     const CardKey *d_card = nullptr;         // device: 64 entries by bit position
     const uint32_t *d_nib = nullptr;         // device: dense class index -> nibble key
-    const void *d_stream_blob = nullptr;     // device: shared-memory image of the streaming kernel (K1)
-    StreamHash stream_hash{};                // its multipliers
+    StreamImage img7, img56;                 // device: shared-memory images of the streaming kernel (K1): river; flop / turn
+    const uint32_t *d_class_nib = nullptr;   // device: global class id -> nibble key (N_HAND_CLASSES, ascending)
     const CardKey *h_card = nullptr;         // host copy of d_card
     CatBase cat_base{};
     uint32_t n_classes = 0;

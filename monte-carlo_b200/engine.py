@@ -10,7 +10,10 @@ LIB_PATH = os.path.join(_HERE, "libmcpoker.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 MC_OK, MC_ERR_INVALID, MC_ERR_NOT_INIT, MC_ERR_CUDA, MC_ERR_NO_DEVICE, MC_ERR_TOO_FEW = 0, -1, -2, -3, -4, -5
-KEY_NIBBLE, KEY_PACKED, KEY_NIBBLE_FLO, KEY_NIBBLE_TABLE, KEY_NIBBLE_HASH = 0, 1, 2, 3, 4
+KEY_NIBBLE, KEY_PACKED, KEY_NIBBLE_FLO, KEY_NIBBLE_TABLE, KEY_NIBBLE_HASH, KEY_CLASS16 = 0, 1, 2, 3, 4, 5
+IN_MASK64, IN_PACKED48, IN_COLEX32 = 0, 1, 2
+CLASS_INVALID = 0xFFFF
+N_HAND_CLASSES = 7462
 KEY_INVALID = 0xFFFFFFFF
 MAX_SEATS = 9
 N_CLASSES = 169
@@ -19,7 +22,8 @@ EXPORTS = [
     "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version",
     "mc_card_bit", "mc_key_packed_to_nibble", "mc_key_decode",
     "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval_batch_packed48", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
-    "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_random_hands", "mc_random_hands_dev",
+    "mc_eval_batch", "mc_eval_batch_colex32", "mc_eval_batch_dev", "mc_unrank_colex32_dev", "mc_class_keys",
+    "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_end_game", "mc_random_hands", "mc_random_hands_dev",
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
     "mc_equity_mc", "mc_equity_mc_dev", "mc_equity_ranges", "mc_preflop_matrix", "mc_preflop_matrix_part", "mc_preflop_cells",
@@ -73,7 +77,13 @@ def lib():
     L.mc_eval7_batch_dev.argtypes = [vp, sz, vp, vp]
     L.mc_eval7_batch_dev_fmt.argtypes = [vp, sz, vp, C.c_int, vp]
     L.mc_showdown.argtypes = [u64, P(u64), C.c_int, P(u32), P(u32)]
-    L.mc_showdown_groups.argtypes = [u64, P(u64), C.c_int, P(u32), P(i32), P(i32)]
+    L.mc_showdown_groups.argtypes = [u64, P(u64), C.c_int, P(u32), P(i32), P(i32), P(u32)]
+    L.mc_end_game.argtypes = [u64, P(u64), C.c_int, P(i64), P(i32), P(u32), C.c_int, P(u32), P(i32), P(i32), P(u32), P(i64)]
+    L.mc_eval_batch.argtypes = [vp, C.c_int, sz, vp, C.c_int, C.c_int]
+    L.mc_eval_batch_colex32.argtypes = [vp, sz, vp]
+    L.mc_eval_batch_dev.argtypes = [vp, sz, vp, C.c_int, C.c_int, vp]
+    L.mc_unrank_colex32_dev.argtypes = [vp, sz, vp, vp]
+    L.mc_class_keys.argtypes = [vp, C.c_int]
     L.mc_settle_pots.argtypes = [P(i32), C.c_int, P(i64), P(i32), P(u32), C.c_int, P(i64)]
     L.mc_random_hands.argtypes = [u64, u64, sz, C.c_int, vp]
     L.mc_random_hands_dev.argtypes = [u64, u64, sz, C.c_int, vp, vp]

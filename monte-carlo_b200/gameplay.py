@@ -34,12 +34,18 @@ def end_game_ranking(community_cards, hands):                # :127-132
 
 def update_stacks(pots, winners, stacks):                    # :104-116
     """pots: [{bet, n, players(set)}]; winners: tie groups best first; stacks: {id: chips} updated in place.
-    The first tie group that intersects a pot's players splits int(total/|group|) each (:108-112)."""
-    for pot in pots:
-        pot_winners = next((set(pot["players"]) & g for g in winners if set(pot["players"]) & g), None)
-        if not pot_winners:
-            continue
-        share = int((pot["bet"] * pot["n"]) / len(pot_winners))
-        for p in pot_winners:
-            stacks[p] = stacks.get(p, 0) + share
+    The first tie group that intersects a pot's players splits int(total/|group|) each (:108-112) -- settled by
+    mc_settle_pots.  A pot none of whose players is in any group raises (the reference divides by zero there, :112)."""
+    ids = sorted({p for g in winners for p in g} | {p for pot in pots for p in pot["players"]}, key=repr)
+    if len(ids) > 9:
+        raise ValueError("more than nine players")
+    seat = {p: i for i, p in enumerate(ids)}
+    group_of = [-1] * len(ids)
+    for gi, g in enumerate(winners):
+        for p in g:
+            group_of[seat[p]] = gi
+    delta = api.settle_pots(group_of, [(pot["bet"], pot["n"], [seat[p] for p in pot["players"]]) for pot in pots]) if ids else []
+    for p, d in zip(ids, delta):
+        if d or p in stacks:
+            stacks[p] = stacks.get(p, 0) + d
     return stacks

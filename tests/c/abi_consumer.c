@@ -8,7 +8,7 @@
 int main(void) {
     int32_t cat = -1, hit[5], n_hit = 0, kick[5], n_kick = 0;
     uint64_t hist[9];
-    if (mc_abi_version() != 1) return 1;
+    if (mc_abi_version() != 2) return 1;
     /* card id 12 = ace of hearts (COMPLETE-DECK index): suit lane 0, rank 14 */
     if (mc_card_bit(12) != ((uint64_t)1 << 14)) return 2;
     if (mc_card_bit(52) != 0) return 3;

@@ -18,6 +18,20 @@ static int next(int *c, int k, int n) {
     for (int i = 0; i < k; i++) { int lim = (i + 1 < k) ? c[i + 1] : n; if (c[i] + 1 < lim) { c[i]++; for (int j = 0; j < i; j++) c[j] = j; return 1; } }
     return 0;
 }
+// one hand through a stream image, step by step as k1h_fast (kernels.cu) does it
+template <class LAY>
+static uint32_t stream_lookup(const std::vector<unsigned char> &img, const mcp::StreamHash &SH, uint64_t m) {
+    auto rd32 = [&](uint32_t a) { uint32_t v; memcpy(&v, img.data() + a, 4); return v; };
+    auto rd16 = [&](uint32_t a) { uint16_t v; memcpy(&v, img.data() + a, 2); return (uint32_t)v; };
+    uint32_t c0, c1, c2;
+    mcp::sh_planes((uint32_t)m, (uint32_t)(m >> 32), &c0, &c1, &c2);
+    const uint32_t t = mcp::sh_t(c0, c1, c2, SH), bk = mcp::sh_bucket(mcp::sh_b(c0, c1, c2, SH));
+    uint32_t fm = 0;
+    for (int s4 = 0; s4 < 4; s4++) { uint32_t lane = (uint32_t)(m >> (16 * s4)) & 0xFFFFu; if (__builtin_popcount(lane) >= 5) fm = lane; }
+    uint32_t ka = rd16(LAY::V_OFF + 2u * mcp::sh_slot<LAY>(t) + rd16(LAY::D_OFF + 2u * bk));   // D' is in bytes
+    if (fm) ka = rd16(LAY::F_OFF + 2u * (fm >> 2));
+    return rd32(ka);
+}
 // mode 2: the additive-key / perfect-hash evaluator (hashtab.cuh + hashtab_build.h) on every 7-card hand.
 // The representatives are evaluated here with eval.cuh compiled for the host; in the product mc_init does it on the GPU.
 static int check_hash() {
@@ -33,24 +47,43 @@ static int check_hash() {
     }
     if (!err.empty()) { fprintf(stderr, "ht_build: %s\n", err.c_str()); return 1; }
     printf("hash tables: mul=%08x classes=%zu reps=%zu\n", T.mul, T.nib_keys.size(), reps.size());
-    // the shared-memory image of the streaming kernel (K1), read here exactly as k1h_fast reads it
-    std::vector<unsigned char> sb;
-    mcp::StreamHash SH;
-    err = mcp::ht_build_stream_blob(T, &sb, &SH);
-    if (!err.empty()) { fprintf(stderr, "ht_build_stream_blob: %s\n", err.c_str()); return 1; }
-    printf("stream hash multipliers: %08x %08x %08x %08x\n", SH.m1, SH.m2, SH.m3, SH.m4);
-    auto rd32 = [&](uint32_t a) { uint32_t v; memcpy(&v, sb.data() + a, 4); return v; };
-    auto rd16 = [&](uint32_t a) { uint16_t v; memcpy(&v, sb.data() + a, 2); return (uint32_t)v; };
-    auto stream_key = [&](uint64_t m) -> uint32_t {
-        uint32_t c0, c1, c2;
-        mcp::sh_planes((uint32_t)m, (uint32_t)(m >> 32), &c0, &c1, &c2);
-        const uint32_t t = mcp::sh_t(c0, c1, c2, SH), bk = mcp::sh_bucket(mcp::sh_b(c0, c1, c2, SH));
-        uint32_t fm = 0;
-        for (int s4 = 0; s4 < 4; s4++) { uint32_t lane = (uint32_t)(m >> (16 * s4)) & 0xFFFFu; if (__builtin_popcount(lane) >= 5) fm = lane; }
-        uint32_t ka = rd16(mcp::SB_V_OFF + 2u * (t >> 16) + rd16(mcp::SB_D_OFF + 2u * bk));   // D' is in bytes
-        if (fm) ka = rd16(mcp::sb_flush_addr(fm >> 2));
-        return rd32(ka);
-    };
+    // the shared-memory images of the streaming kernel (K1), read here exactly as k1h_fast reads them
+    std::vector<mcp::StreamRep> sreps;
+    mcp::ht_stream_representatives(&sreps);
+    std::vector<uint32_t> spacked(sreps.size());
+    for (size_t i = 0; i < sreps.size(); i++) spacked[i] = mcp::eval_packed(sreps[i].mask);
+    static mcp::StreamImages IM;
+    err = mcp::ht_build_stream_images(sreps, spacked, &IM);
+    if (!err.empty()) { fprintf(stderr, "ht_build_stream_images: %s\n", err.c_str()); return 1; }
+    printf("stream hash multipliers: %08x %08x %08x %08x / %08x %08x %08x %08x, %zu classes\n", IM.h7.m1, IM.h7.m2, IM.h7.m3, IM.h7.m4,
+           IM.h56.m1, IM.h56.m2, IM.h56.m3, IM.h56.m4, IM.class_nib.size());
+    const mcp::StreamHash SH = IM.h7;
+    const std::vector<unsigned char> &sb = IM.key7;
+    auto stream_key = [&](uint64_t m) -> uint32_t { return stream_lookup<mcp::Lay7>(sb, SH, m); };
+    // flop / turn images: every 5- and 6-card hand through Lay56, key flavour and class flavour
+    for (int k = 5; k <= 6; k++) {
+        uint64_t tot = BINOM[52][k], bad56 = 0;
+#pragma omp parallel for reduction(+ : bad56) schedule(static, 1)
+        for (int th = 0; th < 64; th++) {
+            uint64_t chunk = (tot + 63) / 64, lo = chunk * th, hi = lo + chunk > tot ? tot : lo + chunk;
+            if (lo >= hi) continue;
+            int c[7]; unrank(lo, k, c);
+            for (uint64_t i = lo; i < hi; i++) {
+                uint64_t m = 0;
+                for (int j = 0; j < k; j++) m |= 1ull << (16 * (c[j] / 13) + c[j] % 13 + 2);
+                const uint32_t want = orc_eval_mask(m);
+                const uint32_t gid = stream_lookup<mcp::Lay56>(IM.cls56, IM.h56, m);
+                if (stream_lookup<mcp::Lay56>(IM.key56, IM.h56, m) != want || gid >= IM.class_nib.size() || IM.class_nib[gid] != want) {
+                    if (bad56 < 5) fprintf(stderr, "LAY56 MISMATCH mask=%016llx\n", (unsigned long long)m);
+                    bad56++;
+                }
+                next(c, k, 52);
+            }
+        }
+        printf("k=%d deck=52 hands=%llu mismatches=%llu (Lay56 stream images)\n", k, (unsigned long long)tot, (unsigned long long)bad56);
+        if (bad56) return 1;
+    }
+    for (size_t i = 1; i < IM.class_nib.size(); i++) if (IM.class_nib[i - 1] >= IM.class_nib[i]) { fprintf(stderr, "class keys not ascending\n"); return 1; }
     uint64_t total = BINOM[52][7], kbad = 0;
 #pragma omp parallel for reduction(+ : kbad) schedule(static, 1)
     for (int th = 0; th < 64; th++) {
@@ -64,6 +97,8 @@ static int check_hash() {
             const uint32_t got = T.nib_keys[T.cat_base[code >> 12] + (code & 0xFFFu)];
             const uint32_t want = orc_eval_mask(m);
             if (stream_key(m) != want) { if (kbad < 5) fprintf(stderr, "STREAM BLOB MISMATCH mask=%016llx\n", (unsigned long long)m); kbad++; }
+            const uint32_t gid = stream_lookup<mcp::Lay7>(IM.cls7, SH, m);
+            if (gid >= IM.class_nib.size() || IM.class_nib[gid] != want) { if (kbad < 5) fprintf(stderr, "CLASS IMAGE MISMATCH mask=%016llx\n", (unsigned long long)m); kbad++; }
             if (got != want) { if (kbad < 5) fprintf(stderr, "HASH MISMATCH mask=%016llx want=%06x got=%06x code=%04x\n", (unsigned long long)m, want, got, code); kbad++; }
             next(c, 7, 52);
         }

@@ -182,13 +182,78 @@ def test_eval_batch_packed48_rejects_malformed_hands(gpu):
 
 def test_k1_every_seven_card_hand_key_by_key(gpu, oracle):
     """BASELINE target: 100 % bit-exact rank agreement on all 133,784,560 seven-card hands, key by key, through the
-    host-buffer ABI call (the K1 hash kernel for these batch sizes) against the oracle's direct evaluator"""
-    total, step, bad = 133784560, 1 << 24, 0
+    host-buffer ABI calls against the oracle's direct evaluator -- once as masks in / nibble keys out (mc_eval7_batch)
+    and once in the compact wire format, colex ranks in / class ids out (mc_eval_batch_colex32: ranks first..first+n-1
+    ARE the hands of the oracle's colex enumeration)"""
+    total, step, bad, bad_c = 133784560, 1 << 24, 0, 0
+    class_keys = gpu.api.class_keys()
     for first in range(0, total, step):
         n = min(step, total - first)
         masks = oracle.enumerate_masks(7, first, n)
-        bad += int(np.count_nonzero(gpu.api.eval7_batch(masks) != oracle.eval_batch(masks, 0)))
-    assert bad == 0
+        want = oracle.eval_batch(masks, 0)
+        bad += int(np.count_nonzero(gpu.api.eval7_batch(masks) != want))
+        cls = gpu.api.eval_batch_colex32(np.arange(first, first + n, dtype=np.uint32))
+        bad_c += int(np.count_nonzero(class_keys[cls] != want))
+    assert bad == 0 and bad_c == 0
+
+
+def test_class_keys_are_the_five_card_values(gpu, oracle):
+    """mc_class_keys: the ascending list of all 7,462 distinct five-card values, so class ids order like keys"""
+    ck = gpu.api.class_keys()
+    assert ck.shape == (7462,) and np.all(np.diff(ck.astype(np.int64)) > 0)
+    five = oracle.eval_batch(oracle.enumerate_masks(5, 0, 2598960), 0)
+    assert np.array_equal(ck, np.unique(five))
+    with pytest.raises(gpu.engine.McError):
+        gpu.engine.check(gpu.engine.lib().mc_class_keys(ck.ctypes.data, 4892))
+
+
+def test_flop_and_turn_hands_every_hand_key_by_key(gpu, oracle):
+    """player->hand-value on 5 and 6 cards (hand_evaluator.clj:171 at flop / turn): all C(52,5) and all
+    C(52,6) hands through the flop / turn table image of K1, as keys and as class ids, against the oracle"""
+    E, api = gpu.engine, gpu.api
+    ck = api.class_keys()
+    for k, total in ((5, 2598960), (6, 20358520)):
+        masks = oracle.enumerate_masks(k, 0, total)
+        want = oracle.eval_batch(masks, 0)
+        assert np.array_equal(api.eval_batch(masks, E.IN_MASK64, E.KEY_NIBBLE, k), want)
+        assert np.array_equal(api.eval7_batch(masks), want)                      # stage decided from the first hand
+        cls = api.eval_batch(masks, E.IN_MASK64, E.KEY_CLASS16, 0)
+        assert np.array_equal(ck[cls], want)
+        part = masks[:1_000_001]
+        assert np.array_equal(api.eval_batch(api.pack48(part), E.IN_PACKED48, E.KEY_CLASS16, 0), cls[:1_000_001])
+
+
+def test_eval_batch_every_format_and_stage_hint(gpu, oracle):
+    """mc_eval_batch: {masks, packed48, colex32} x {nibble keys, class ids} x stage hint {0, 5, 6, 7}; a wrong hint or a
+    mixed batch only changes the path inside the kernel (slow path), never the result; ragged sizes; invalid hands"""
+    E, api = gpu.engine, gpu.api
+    ck = api.class_keys()
+    h7 = oracle.random_hands(SEED + 21, 0, 300_001)
+    mixed = np.concatenate([h7[:50_000], oracle.random_hands(SEED, 5, 50_001, 5), oracle.random_hands(SEED, 9, 50_002, 6)])
+    np.random.default_rng(1).shuffle(mixed)
+    for hands in (h7, mixed):
+        want = oracle.eval_batch(hands, 0)
+        for hint in (0, 5, 6, 7):
+            assert np.array_equal(api.eval_batch(hands, E.IN_MASK64, E.KEY_NIBBLE, hint), want)
+            assert np.array_equal(ck[api.eval_batch(hands, E.IN_MASK64, E.KEY_CLASS16, hint)], want)
+            assert np.array_equal(ck[api.eval_batch(api.pack48(hands), E.IN_PACKED48, E.KEY_CLASS16, hint)], want)
+    want7 = oracle.eval_batch(h7, 0)
+    ranks = api.colex_rank(h7)
+    for n in (len(h7), 4097, 33, 3, 2, 1):
+        assert np.array_equal(ck[api.eval_batch_colex32(ranks[:n])], want7[:n])
+        assert np.array_equal(api.eval_batch(ranks[:n], E.IN_COLEX32, E.KEY_NIBBLE, 7), want7[:n])
+    assert api.eval_batch_colex32(np.zeros(0, dtype=np.uint32)).shape == (0,)
+    # ranks past the last combination, invalid masks, the tests' rank-1 hands (no class): MC_CLASS_INVALID / MC_KEY_INVALID
+    bad = np.array([133784560, 133784561, 0xFFFFFFFF, 1 << 27], dtype=np.uint32)
+    assert np.all(api.eval_batch_colex32(bad) == 0xFFFF)
+    assert np.all(api.eval_batch(bad, E.IN_COLEX32, E.KEY_NIBBLE, 7) == 0xFFFFFFFF)
+    assert int(api.eval_batch_colex32(np.array([133784559], dtype=np.uint32))[0]) != 0xFFFF
+    odd = np.array([0, 0b111100, (1 << 64) - 1, oracle.mask_of([(0, 1), (1, 2), (2, 3), (3, 5), (0, 4)])], dtype=np.uint64)
+    assert np.all(api.eval_batch(odd, E.IN_MASK64, E.KEY_CLASS16, 0) == 0xFFFF)
+    with pytest.raises(E.McError):
+        api.eval_batch(h7[:4], 7, E.KEY_NIBBLE, 0)
+    with pytest.raises(E.McError):
+        api.eval_batch(h7[:4], E.IN_MASK64, 9, 0)
 
 
 # ---- K2: exhaustive enumeration (BASELINE config 2) ---------------------------------------------------
@@ -442,6 +507,124 @@ def test_abi_is_thread_safe(gpu, oracle):
     for th in threads:
         th.join()
     assert not errors, errors[:5]
+
+
+def test_end_game_one_call(gpu, oracle):
+    """mc_end_game = end-game of gameplay.clj:122-133: ranking, tie groups and update-stacks (:104-116) in one call,
+    against the oracle's showdown grouping + literal update-stacks on random tables and side-pot structures"""
+    import ctypes as C
+    rng = random.Random(17)
+    for _ in range(60):
+        n_seats, n_board = rng.randint(2, 9), rng.choice([3, 4, 5, 5, 5])
+        ids = rng.sample(range(52), 2 * n_seats + n_board)
+        if rng.random() < 0.3:                                          # force ties: everybody plays a made board
+            board_ids, rest = [8, 9, 10, 11, 12], [i for i in range(13, 52)]
+            ids = rng.sample(rest, 2 * n_seats) + board_ids
+            n_board = 5
+        holes = [gpu.api.mask_of_ids(ids[2 * s:2 * s + 2]) for s in range(n_seats)]
+        board = gpu.api.mask_of_ids(ids[2 * n_seats:])
+        pots = [(rng.randint(1, 500), rng.randint(1, n_seats), rng.sample(range(n_seats), rng.randint(1, n_seats)))
+                for _ in range(rng.randint(0, 4))]
+        keys, winners, group_of, n_groups, delta = gpu.api.end_game(board, holes, pots)
+        want = [oracle.lib().orc_eval_mask(board | h) for h in holes]
+        g = (C.c_int * n_seats)()
+        ng = oracle.lib().orc_group_winners((C.c_uint32 * n_seats)(*want), n_seats, g)
+        assert keys == want and list(g) == group_of and ng == n_groups
+        sets = [sum(1 << s for s in range(n_seats) if g[s] == k) for k in range(ng)]
+        stack = (C.c_longlong * 32)()
+        rc = oracle.lib().orc_update_stacks((C.c_uint * ng)(*sets), ng, (C.c_longlong * max(1, len(pots)))(*[p[0] for p in pots]),
+                                            (C.c_int * max(1, len(pots)))(*[p[1] for p in pots]),
+                                            (C.c_uint * max(1, len(pots)))(*[sum(1 << s for s in p[2]) for p in pots]), len(pots), stack)
+        assert rc == 0 and delta == list(stack[:n_seats])
+        assert winners == sets[0]
+
+
+def test_lifecycle_is_safe_against_calls_in_flight(gpu, oracle):
+    """the header's promise: mc_init* / mc_shutdown wait for calls in flight and calls never run on a context that is
+    being torn down.  Four threads hammer compute calls (batch, single-hand ticket path, equity) while a fifth cycles
+    mc_shutdown / mc_init; every call either returns the right answer or fails with MC_ERR_NOT_INIT."""
+    import threading
+    import time
+    E, api = gpu.engine, gpu.api
+    L = E.lib()
+    masks = oracle.random_hands(SEED + 5, 0, 30000)
+    want = oracle.eval_batch(masks, 0)
+    holes = [api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50])]
+    errors, done, stop = [], [0], threading.Event()
+
+    def call(fn):
+        try:
+            return fn()
+        except E.McError as e:
+            if e.code != E.MC_ERR_NOT_INIT:
+                errors.append(repr(e))
+            return None
+
+    def worker(k):
+        it = 0
+        while not stop.is_set():
+            it += 1
+            lo = (k * 997 + it * 131) % 20000
+            got = call(lambda: api.eval7_batch(masks[lo:lo + 5000]))
+            if got is not None and not np.array_equal(got, want[lo:lo + 5000]):
+                errors.append("batch %d/%d" % (k, it))
+            got = call(lambda: api.eval_cards([0, 0, 0, 0, 0], [9, 8, 7, 6, 5]))
+            if got is not None and got != 0x898765:
+                errors.append("single %d/%d: %x" % (k, it, got))
+            got = call(lambda: api.equity_exhaustive(holes))
+            if got is not None and (got[0][0], got[0][1], got[1][0]) != (1388072, 318176, 6056):
+                errors.append("equity %d/%d" % (k, it))
+            got = call(lambda: api.showdown(api.mask_of_ids([8, 9, 10, 11, 12]), [api.mask_of_ids([13, 14]), api.mask_of_ids([26, 27])]))
+            if got is not None and (got[1], got[2]) != (3, [0, 0]):
+                errors.append("showdown %d/%d" % (k, it))
+            done[0] += 1
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for th in threads:
+        th.start()
+    try:
+        for _ in range(6):
+            time.sleep(0.05)
+            L.mc_shutdown()
+            time.sleep(0.02)
+            E.check(L.mc_init(0, 0))
+    finally:
+        time.sleep(0.1)
+        stop.set()
+        for th in threads:
+            th.join()
+        E.check(L.mc_init(0, 0))                                      # leave the session fixture's engine initialised
+    assert not errors, errors[:5]
+    assert done[0] > 0
+
+
+def test_multi_device_split_equals_one_device(gpu, oracle):
+    """the host-buffer calls split their work over every device of the library instance (single-process mode for a JVM
+    host): mc_init(0) on a multi-GPU box must give exactly what mc_init_devices({0}) gives.  Skipped on a 1-GPU box."""
+    import ctypes as C
+    import torch
+    E, api = gpu.engine, gpu.api
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two devices")
+    masks = oracle.random_hands(SEED + 31, 0, 3_000_001)
+    holes9 = [api.mask_of_ids([12, 25])] + [0] * 8
+
+    def everything():
+        return (api.eval7_batch(masks), api.eval_batch_colex32(api.colex_rank(masks)), api.eval_batch_packed48(api.pack48(masks)),
+                api.enumerate7(5, 3_000_000), api.equity_exhaustive([api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50])]),
+                api.equity_mc(holes9, 0, 0, SEED, 7, 1 << 20), api.preflop_cells([(168, 154), (100, 7)]).tolist())
+    try:
+        assert E.init(devices=[0]) == 1
+        one = everything()
+        assert E.init() == torch.cuda.device_count()
+        many = everything()
+    finally:
+        E.init()
+    for a, b in zip(one, many):
+        if isinstance(a, np.ndarray):
+            assert np.array_equal(a, b)
+        else:
+            assert a == b
 
 
 def test_equity_ranges_vs_oracle(gpu, oracle):

@@ -20,7 +20,7 @@ def test_library_loads_and_exports_every_declared_symbol(pkg):
     assert declared == set(pkg.engine.EXPORTS)
     for name in declared:
         assert hasattr(L, name), name
-    assert L.mc_abi_version() == 1
+    assert L.mc_abi_version() == 2
 
 
 def test_header_is_plain_c_and_links(pkg, tmp_path):
@@ -57,6 +57,21 @@ def test_pack48_wire_format(pkg, oracle):
     assert int(p[0]) & 63 == lowest
     with pytest.raises(ValueError):
         pkg.api.pack48(np.array([0xFF00FF], dtype=np.uint64))
+
+
+def test_colex_rank_wire_format(pkg, oracle):
+    """api.colex_rank (what a caller of mc_eval_batch_colex32 computes): rank of the i-th hand of the oracle's colex
+    enumeration is i; random hands round-trip through the oracle's enumeration"""
+    import numpy as np
+    for first in (0, 1_000_000, 133784560 - 5000):
+        masks = oracle.enumerate_masks(7, first, 5000)
+        assert np.array_equal(pkg.api.colex_rank(masks), np.arange(first, first + 5000, dtype=np.uint32))
+    rnd = oracle.random_hands(7, 0, 2000)
+    ranks = pkg.api.colex_rank(rnd)
+    back = np.array([oracle.enumerate_masks(7, int(r), 1)[0] for r in ranks[:200]], dtype=np.uint64)
+    assert np.array_equal(back, rnd[:200])
+    with pytest.raises(ValueError):
+        pkg.api.colex_rank(oracle.random_hands(7, 0, 10, 6))
 
 
 def test_no_gpu_means_loud_failure_not_fallback(pkg):

@@ -19,19 +19,19 @@ d = torch.empty(n, dtype=torch.int64, device="cuda")
 E.check(L.mc_random_hands_dev(0x5EED5EED, 0, n, 7, d.data_ptr(), st))
 h_masks = torch.empty(n, dtype=torch.int64).pin_memory()
 h_masks.copy_(d)
-m, h = d.clone(), torch.zeros(n, dtype=torch.int64, device="cuda")
-for k in range(7):
-    low = m & -m
-    h |= (torch.log2(low.double()) + 0.5).long() << (6 * k)
-    m &= m - 1
+import bench  # noqa: E402
 h_pk = torch.empty(6 * n, dtype=torch.uint8).pin_memory()
-h_pk.copy_(h.view(torch.uint8).reshape(-1, 8)[:, :6].reshape(-1))
+h_pk.copy_(bench.packed48_dev(torch, d))
+h_rk = torch.empty(n, dtype=torch.int32).pin_memory()
+h_rk.copy_(bench.colex_ranks_dev(torch, d))
+c3 = torch.empty(n, dtype=torch.int16).pin_memory()
 k1 = torch.empty(n, dtype=torch.int32).pin_memory()
 k2 = torch.empty(n, dtype=torch.int32).pin_memory()
 torch.cuda.synchronize()
 res = {}
 for name, fn in (("mask", lambda: E.check(L.mc_eval7_batch(h_masks.data_ptr(), n, k1.data_ptr()))),
-                 ("packed48", lambda: E.check(L.mc_eval_batch_packed48(h_pk.data_ptr(), n, k2.data_ptr())))):
+                 ("packed48", lambda: E.check(L.mc_eval_batch_packed48(h_pk.data_ptr(), n, k2.data_ptr()))),
+                 ("colex32", lambda: E.check(L.mc_eval_batch_colex32(h_rk.data_ptr(), n, c3.data_ptr())))):
     fn()
     best = 1e9
     for _ in range(5):
@@ -39,5 +39,5 @@ for name, fn in (("mask", lambda: E.check(L.mc_eval7_batch(h_masks.data_ptr(), n
         fn()
         best = min(best, time.perf_counter() - t0)
     res[name] = n / best / 1e9
-print("%d device(s) in one process, 2^%d hands, stage 2^%s: mask %.2f G evals/s, packed48 %.2f G evals/s, equal %s" % (
-    ndev, n.bit_length() - 1, os.environ.get("MCP_STAGE_LOG2", "22"), res["mask"], res["packed48"], torch.equal(k1, k2)))
+print("%d device(s) in one process, 2^%d hands, stage 2^%s: mask %.2f, packed48 %.2f, colex32 %.2f G evals/s, equal %s" % (
+    ndev, n.bit_length() - 1, os.environ.get("MCP_STAGE_LOG2", "22"), res["mask"], res["packed48"], res["colex32"], torch.equal(k1, k2)))
