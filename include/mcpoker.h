@@ -73,6 +73,7 @@ extern "C" {
 #define MC_IN_COLEX32       2   /* uint32 colex rank of a 7-card hand over card ids, 4 B per hand */
 
 #define MC_MAX_SEATS        9
+#define MC_MAX_POTS         8   /* side pots of the EV calls */
 #define MC_N_CLASSES        169
 
 /* ---- lifecycle ---------------------------------------------------------------------------------- */
@@ -161,6 +162,16 @@ int  mc_equity_exhaustive_dev(const uint64_t *hole_masks /* host */, int n_seats
                               uint64_t dead_mask, uint64_t first_board, uint64_t n_boards_in,
                               int64_t *d_counts, void *stream);
 
+/* EV: the same enumeration with the reference's pot settlement applied to every board (update-stacks
+ * gameplay.clj:104-116 over the Bet records of bet.clj:7-8; pots exactly as in mc_settle_pots).  Every seat of a
+ * simulation is at the showdown, so for each pot the seats of pot_players holding its best hand receive
+ * int(bet * n / their number) each (:110-112, the remainder is dropped as the reference drops it).  chips[seat] = the sum
+ * over all boards of what the seat receives: EV = chips / n_boards minus what the seat put in.  1 <= n_pots <=
+ * MC_MAX_POTS, every pot's players a non-empty subset of the seats, all pots together fewer than 2^31 chips. */
+int  mc_equity_exhaustive_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                             const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots,
+                             int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips, uint64_t *n_boards);
+
 /* ---- Monte Carlo equity (K4) -------------------------------------------------------------------- */
 /* hole mask 0 = random seat.  Trial t depends only on (seed, t): any split of [first, first+n) over
  * devices / processes / calls sums to the same counts. */
@@ -170,6 +181,17 @@ int  mc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, 
 int  mc_equity_mc_dev(const uint64_t *hole_masks /* host */, int n_seats, uint64_t board_mask, uint64_t dead_mask,
                       uint64_t seed, uint64_t first_trial, uint64_t n_trials,
                       int64_t *d_counts /* 27 int64, accumulated into */, void *stream);
+
+/* EV by Monte Carlo: as mc_equity_exhaustive_ev, per trial.  d_counts of the _dev form: 36 int64 = win[9] tie[9] loss[9]
+ * chips[9], accumulated into. */
+int  mc_equity_mc_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                     uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                     const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots,
+                     int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips);
+int  mc_equity_mc_ev_dev(const uint64_t *hole_masks /* host */, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                         uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                         const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots,
+                         int64_t *d_counts /* 36 int64, accumulated into */, void *stream);
 
 /* ---- heads-up range vs range on a (partial) board ------------------------------------- */
 /* A hole is indexed by the colex rank of its two card ids: idx = c0 + c1*(c1-1)/2, c0 < c1 (0..1325).  Every pair of

@@ -229,6 +229,31 @@ def equity_mc(hole_masks, board_mask, dead_mask, seed, first_trial, n_trials):
     return list(w[:n]), list(t[:n]), list(l[:n])
 
 
+def equity_exhaustive_ev(hole_masks, pots, board_mask=0, dead_mask=0):
+    """exhaustive equity + the reference's pot settlement per board: pots = [(bet, n, [seats])] ->
+    (win, tie, loss, chips per seat summed over all boards, number of boards)"""
+    E.ensure_init()
+    n = len(hole_masks)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    w, t, l = _seat_arrays(n)
+    chips, nb = (C.c_int64 * 9)(), C.c_uint64(0)
+    bet, cnt, msk, k = _pot_arrays(pots)
+    E.check(E.lib().mc_equity_exhaustive_ev(h, n, board_mask, dead_mask, bet, cnt, msk, k, w, t, l, chips, C.byref(nb)))
+    return list(w[:n]), list(t[:n]), list(l[:n]), list(chips[:n]), nb.value
+
+
+def equity_mc_ev(hole_masks, pots, board_mask, dead_mask, seed, first_trial, n_trials):
+    """Monte Carlo equity + the reference's pot settlement per trial -> (win, tie, loss, chips per seat summed over the trials)"""
+    E.ensure_init()
+    n = len(hole_masks)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    w, t, l = _seat_arrays(n)
+    chips = (C.c_int64 * 9)()
+    bet, cnt, msk, k = _pot_arrays(pots)
+    E.check(E.lib().mc_equity_mc_ev(h, n, board_mask, dead_mask, seed, first_trial, n_trials, bet, cnt, msk, k, w, t, l, chips))
+    return list(w[:n]), list(t[:n]), list(l[:n]), list(chips[:n])
+
+
 def hole_index(card_a, card_b):
     """colex rank of a two-card hole over card ids (0..1325)"""
     c0, c1 = min(card_a, card_b), max(card_a, card_b)

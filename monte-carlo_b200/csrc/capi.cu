@@ -330,6 +330,26 @@ int check_equity_args(const uint64_t *hole_masks, int n_seats, uint64_t board, u
     return MC_OK;
 }
 
+// pots of the EV calls -> PotArgs (kernels.cuh)
+int check_pots(const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots, int n_seats, PotArgs *out) {
+    if (n_pots < 1 || n_pots > MC_MAX_POTS) return fail(MC_ERR_INVALID, "n_pots must be 1..MC_MAX_POTS");
+    if (!pot_bet || !pot_n || !pot_players) return fail(MC_ERR_INVALID, "null pot array");
+    *out = PotArgs{};
+    out->n_pots = n_pots;
+    int64_t sum = 0;
+    for (int p = 0; p < n_pots; p++) {
+        if (pot_bet[p] < 0 || pot_n[p] < 0) return fail(MC_ERR_INVALID, "negative pot");
+        const unsigned __int128 tot = (unsigned __int128)(uint64_t)pot_bet[p] * (uint64_t)pot_n[p];
+        if (tot > 0x7FFFFFFFull) return fail(MC_ERR_INVALID, "the pots of a simulation must hold fewer than 2^31 chips in total");
+        sum += (int64_t)tot;
+        if (sum > 0x7FFFFFFFll) return fail(MC_ERR_INVALID, "the pots of a simulation must hold fewer than 2^31 chips in total");
+        if (pot_players[p] == 0 || (pot_players[p] >> n_seats)) return fail(MC_ERR_INVALID, "a pot's players must be a non-empty set of the seats (the reference divides by zero on an empty one, gameplay.clj:112)");
+        out->players[p] = pot_players[p];
+        out->total[p] = (uint32_t)tot;
+    }
+    return MC_OK;
+}
+
 // run fn(ctx, lo, hi) on every device over an even split of [0, total), then sum `words` u64 of d_small
 template <typename F>
 int sharded_small_job(uint64_t total, int words, unsigned long long *sum, F launch) {
@@ -766,7 +786,76 @@ int mc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t board
     return mc_equity_exhaustive_range(hole_masks, n_seats, board_mask, dead_mask, 0, total, win, tie, loss);
 }
 
+int mc_equity_exhaustive_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                            const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots,
+                            int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips, uint64_t *n_boards) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, false, &a, nullptr);
+    if (rc) return rc;
+    PotArgs pots;
+    rc = check_pots(pot_bet, pot_n, pot_players, n_pots, n_seats, &pots);
+    if (rc) return rc;
+    const uint64_t total = board_count(a);
+    if (n_boards) *n_boards = total;
+    unsigned long long sum[36];
+    rc = sharded_small_job(total, 36, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        CU(launch_equity_exhaustive_hash(a, lo, cnt, reinterpret_cast<long long *>(c.d_small), c.tb, c.info, c.stream, &pots));
+        return MC_OK;
+    });
+    if (rc) return rc;
+    for (int s = 0; s < n_seats; s++) {
+        if (win) win[s] = (int64_t)sum[s];
+        if (tie) tie[s] = (int64_t)sum[9 + s];
+        if (loss) loss[s] = (int64_t)sum[18 + s];
+        if (chips) chips[s] = (int64_t)sum[27 + s];
+    }
+    return MC_OK;
+}
+
 // ---- K4 ---------------------------------------------------------------------------------------------
+int mc_equity_mc_ev_dev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                        uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                        const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots,
+                        int64_t *d_counts, void *stream) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, true, &a, nullptr);
+    if (rc) return rc;
+    PotArgs pots;
+    rc = check_pots(pot_bet, pot_n, pot_players, n_pots, n_seats, &pots);
+    if (rc) return rc;
+    if (!d_counts) return fail(MC_ERR_INVALID, "null device buffer");
+    std::shared_lock<std::shared_mutex> life(g_life);
+    DeviceInfo di; const DeviceTables *tb;
+    rc = current_tables(&di, &tb);
+    if (rc) return rc;
+    if (n_trials) CU(launch_equity_mc_fy(a, seed, first_trial, n_trials, reinterpret_cast<long long *>(d_counts), *tb, di, (cudaStream_t)stream, &pots));
+    return MC_OK;
+}
+int mc_equity_mc_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                    uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                    const int64_t *pot_bet, const int32_t *pot_n, const uint32_t *pot_players, int n_pots,
+                    int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips) {
+    EquityArgs a;
+    int rc = check_equity_args(hole_masks, n_seats, board_mask, dead_mask, true, &a, nullptr);
+    if (rc) return rc;
+    PotArgs pots;
+    rc = check_pots(pot_bet, pot_n, pot_players, n_pots, n_seats, &pots);
+    if (rc) return rc;
+    unsigned long long sum[36];
+    rc = sharded_small_job(n_trials, 36, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        CU(launch_equity_mc_fy(a, seed, first_trial + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.tb, c.info, c.stream, &pots));
+        return MC_OK;
+    });
+    if (rc) return rc;
+    for (int s = 0; s < n_seats; s++) {
+        if (win) win[s] = (int64_t)sum[s];
+        if (tie) tie[s] = (int64_t)sum[9 + s];
+        if (loss) loss[s] = (int64_t)sum[18 + s];
+        if (chips) chips[s] = (int64_t)sum[27 + s];
+    }
+    return MC_OK;
+}
+
 int mc_equity_mc_dev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
                      uint64_t seed, uint64_t first_trial, uint64_t n_trials, int64_t *d_counts, void *stream) {
     EquityArgs a;

@@ -40,6 +40,15 @@ struct EquityArgs {
     uint64_t dead;
     int n_seats;
 };
+// Side-pot structure for the EV variants of K3 / K4 (update-stacks gameplay.clj:104-116 over the Bet records of
+// bet.clj:7-8): pot p holds total[p] = bet * n chips and is played for by the seats of players[p] (bitmask); per trial
+// the seats of the pot that hold its best hand receive floor(total / their number) each (:110-112).
+constexpr int MAX_POTS = 8;
+struct PotArgs {
+    int n_pots = 0;
+    uint32_t players[MAX_POTS] = {};
+    uint32_t total[MAX_POTS] = {};             // chips in the pot; the totals of all pots sum below 2^31
+};
 // one warp: keys per seat, winner bitmask, tie-group index per seat, number of groups
 // d_out: uint32 keys[9], uint32 winners, int32 group_of[9], int32 n_groups  (20 words)
 // d_out of these two may be device-mapped pinned host memory: after the results the kernel writes `ticket` into
@@ -67,10 +76,13 @@ struct DeviceTables {
 };
 cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out /* hist[9], nibble key sum */,
                               const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+// d_counts: win[9] tie[9] loss[9] (27 int64, accumulated into); with pots (n_pots > 0) also chips[9] at [27..36)
 cudaError_t launch_equity_exhaustive_hash(const EquityArgs &a, uint64_t first_board, uint64_t n_boards, long long *d_counts,
-                                          const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+                                          const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st,
+                                          const PotArgs *pots = nullptr);
 cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
-                                long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+                                long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st,
+                                const PotArgs *pots = nullptr);
 cudaError_t launch_preflop_hash(const Matchup *d_matchups, int n_matchups, long long *d_wtl,
                                 const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
 

@@ -103,6 +103,71 @@ struct Tally {
     }
 };
 
+// ---------------------------------------------------------------------------------------------------
+// EV: the reference's pot settlement per trial (update-stacks gameplay.clj:104-116; every seat of a simulation is at the
+// showdown, so "the first tie group that intersects the pot" is the set of its seats holding the pot's best hand).
+// Class codes are 16-bit: k1 = code | 0x10000 marks a seat, `in` (0x1FFFF or 0) keeps it if it plays for the pot, and
+// masked + (0x20000 - best) carries into bit 17 exactly for the pot's seats at its maximum -- no compares.  The share
+// floor(total / k) comes from a table built on the host (no division here); chips go to 32-bit per-thread accumulators
+// that are folded into 64-bit shared counters before they can wrap (flush_every trials, computed from the totals).
+// ---------------------------------------------------------------------------------------------------
+struct PotParams {
+    uint32_t in[MAX_POTS][MAX_SEATS];          // by kernel seat
+    uint32_t share[MAX_POTS][MAX_SEATS + 1];   // share[p][k] = floor(total / k), k = 1..9
+    int n_pots;
+    uint32_t flush_every;
+};
+template <int NSLOT>
+__device__ __forceinline__ void pots_settle(const PotParams &pp, const uint32_t (&key)[NSLOT], uint32_t (&chips)[NSLOT]) {
+    uint32_t k1[NSLOT];
+#pragma unroll
+    for (int s = 0; s < NSLOT; s++) k1[s] = key[s] | 0x10000u;
+#pragma unroll
+    for (int p = 0; p < MAX_POTS; p++) {
+        if (p < pp.n_pots) {
+            uint32_t mk[NSLOT], best = 0;
+#pragma unroll
+            for (int s = 0; s < NSLOT; s++) { mk[s] = k1[s] & pp.in[p][s]; best = max(best, mk[s]); }
+            const uint32_t cb = 0x20000u - best;
+            uint32_t at[NSLOT], k = 0;
+#pragma unroll
+            for (int s = 0; s < NSLOT; s++) { at[s] = (mk[s] + cb) >> 17; k += at[s]; }
+            const uint32_t share = pp.share[p][k];
+#pragma unroll
+            for (int s = 0; s < NSLOT; s++) chips[s] += at[s] * share;
+        }
+    }
+}
+// per-thread fold inside a loop whose trip count differs between the lanes of a warp: plain shared atomics
+template <int NSLOT>
+__device__ __forceinline__ void chips_fold_thread(uint32_t (&chips)[NSLOT], unsigned long long *schips) {
+#pragma unroll
+    for (int s = 0; s < NSLOT; s++) { if (chips[s]) atomicAdd(&schips[s], (unsigned long long)chips[s]); chips[s] = 0; }
+}
+// final fold, every lane of the warp present: two 16-bit halves through REDUX, one shared atomic per seat and warp
+template <int NSLOT>
+__device__ __forceinline__ void chips_fold_warp(const uint32_t (&chips)[NSLOT], unsigned long long *schips) {
+#pragma unroll
+    for (int s = 0; s < NSLOT; s++) {
+        const uint32_t lo = warp_sum(chips[s] & 0xFFFFu), hi = warp_sum(chips[s] >> 16);
+        if ((threadIdx.x & 31) == 0 && (lo | hi)) atomicAdd(&schips[s], (unsigned long long)lo + ((unsigned long long)hi << 16));
+    }
+}
+// host: kernel-seat view of the caller's pots.  seat_of[q] = caller seat of kernel seat q (n_kernel_seats of them)
+static void make_pot_params(const PotArgs *pots, const int *seat_of, int n_kernel_seats, PotParams *pp) {
+    memset(pp, 0, sizeof *pp);
+    if (!pots) return;
+    pp->n_pots = pots->n_pots;
+    uint64_t sum = 0;
+    for (int p = 0; p < pots->n_pots; p++) {
+        for (int q = 0; q < n_kernel_seats; q++) pp->in[p][q] = ((pots->players[p] >> seat_of[q]) & 1u) ? 0x1FFFFu : 0u;
+        for (int k = 1; k <= MAX_SEATS; k++) pp->share[p][k] = pots->total[p] / (uint32_t)k;
+        sum += pots->total[p];
+    }
+    const uint64_t f = sum ? 0xFFFFFFFFull / sum : 0xFFFFFFFFull;
+    pp->flush_every = (uint32_t)(f > 0x7FFFFFFFull ? 0x7FFFFFFFull : (f < 1 ? 1 : f));
+}
+
 constexpr int HASH_THREADS = 512;
 constexpr int LIVE_MAX = 56;
 
@@ -134,11 +199,12 @@ struct EqxHashParams {
     uint64_t first, count;
     int n_seats, n_live;
     uint4 live[LIVE_MAX];               // ascending bit position; entries >= n_live are zero
+    PotParams pots;                     // EV variant only
 };
 
 template <int NS> constexpr int eqx_threads() { return NS == 2 ? 1024 : HASH_THREADS; }   // heads-up needs <= 51 registers
 
-template <int K, int NS>
+template <int K, int NS, bool EV>
 __global__ void __launch_bounds__(eqx_threads<NS>(), 1)
 equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob *__restrict__ g_blob,
                        long long *__restrict__ d_counts) {
@@ -146,18 +212,21 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
     HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
     uint4 *slive = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));
     uint32_t *sbin = reinterpret_cast<uint32_t *>(slive + LIVE_MAX);
-    __shared__ unsigned long long sred[19];
+    __shared__ unsigned long long sred[19 + MAX_SEATS];
     __shared__ unsigned long long mbar;
     BulkStage stage;
     stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
     if (threadIdx.x < LIVE_MAX) slive[threadIdx.x] = prm.live[threadIdx.x];
-    if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
+    if (threadIdx.x < 19 + MAX_SEATS) sred[threadIdx.x] = 0ull;
     stage.wait();
     const uint32_t tbl = staged_table_base(H);
 
     const int n_seats = prm.n_seats, nl = prm.n_live;
     Tally<NS> tl; tl.clear();
+    uint32_t chips[NS], since = 0;
+#pragma unroll
+    for (int s = 0; s < NS; s++) chips[s] = 0;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t per = (prm.count + nthreads - 1) / nthreads;
     const uint64_t me = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -176,10 +245,19 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
                     key[s] = hb_class(b.t + prm.h_t[s], b.sn + prm.h_sn[s], b.mlo | prm.h_mlo[s], b.mhi | prm.h_mhi[s], tbl);
             }
             tl.add(key, n_seats);
+            if constexpr (EV) {
+                pots_settle<NS>(prm.pots, key, chips);
+                if (++since == prm.pots.flush_every) { chips_fold_thread<NS>(chips, sred + 19); since = 0; }
+            }
             w.next(slive, nl);
         }
     }
+    if constexpr (EV) chips_fold_warp<NS>(chips, sred + 19);
     tl.flush(n_seats, sred, d_counts);
+    if constexpr (EV) {           // (tl.flush has synchronised the block)
+        if ((int)threadIdx.x < n_seats && sred[19 + threadIdx.x])
+            atomicAdd(reinterpret_cast<unsigned long long *>(d_counts) + 27 + threadIdx.x, sred[19 + threadIdx.x]);
+    }
 }
 
 static size_t eqx_smem() { return sizeof(HashBlob) + LIVE_MAX * sizeof(uint4) + BIN_N * BIN_K * sizeof(uint32_t); }
@@ -196,9 +274,9 @@ static HandState state_of(uint64_t mask, const CardKey *card, uint32_t sn0) {
     return h;
 }
 
-template <int K, int NS>
+template <int K, int NS, bool EV>
 static cudaError_t launch_eqx(const EqxHashParams &prm, const HashBlob *blob, long long *d_counts, int grid, cudaStream_t st) {
-    auto kern = equity_exh_hash_kernel<K, NS>;
+    auto kern = equity_exh_hash_kernel<K, NS, EV>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
     if (e != cudaSuccess) return e;
     kern<<<grid, eqx_threads<NS>(), eqx_smem(), st>>>(prm, blob, d_counts);
@@ -206,9 +284,13 @@ static cudaError_t launch_eqx(const EqxHashParams &prm, const HashBlob *blob, lo
 }
 
 cudaError_t launch_equity_exhaustive_hash(const EquityArgs &a, uint64_t first_board, uint64_t n_boards, long long *d_counts,
-                                          const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+                                          const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st, const PotArgs *pots) {
     if (n_boards == 0) return cudaSuccess;
     EqxHashParams prm;
+    const bool ev = pots && pots->n_pots > 0;
+    int ident[MAX_SEATS];
+    for (int s = 0; s < MAX_SEATS; s++) ident[s] = s;
+    make_pot_params(ev ? pots : nullptr, ident, a.n_seats, &prm.pots);
     uint64_t used = a.board | a.dead;
     for (int s = 0; s < MAX_SEATS; s++) {
         const uint64_t h = s < a.n_seats ? a.hole[s] : 0ull;
@@ -220,11 +302,11 @@ cudaError_t launch_equity_exhaustive_hash(const EquityArgs &a, uint64_t first_bo
     prm.first = first_board; prm.count = n_boards; prm.n_seats = a.n_seats;
     fill_live(DECK_MASK & ~used, tb.h_card, prm.live, &prm.n_live);
     const int K = 5 - __builtin_popcountll(a.board);
-    const bool two = a.n_seats == 2;
+    const bool two = a.n_seats == 2 && !ev;               // (the EV variant exists in the general shape only)
     const uint64_t tpb = two ? eqx_threads<2>() : eqx_threads<MAX_SEATS>();
     uint64_t want = (n_boards + tpb - 1) / tpb;
     const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
-#define EQX_CASE(k) case k: return two ? launch_eqx<k, 2>(prm, tb.d_blob, d_counts, grid, st) : launch_eqx<k, MAX_SEATS>(prm, tb.d_blob, d_counts, grid, st)
+#define EQX_CASE(k) case k: return ev ? launch_eqx<k, MAX_SEATS, true>(prm, tb.d_blob, d_counts, grid, st) : two ? launch_eqx<k, 2, false>(prm, tb.d_blob, d_counts, grid, st) : launch_eqx<k, MAX_SEATS, false>(prm, tb.d_blob, d_counts, grid, st)
     switch (K) {
         EQX_CASE(0); EQX_CASE(1); EQX_CASE(2); EQX_CASE(3); EQX_CASE(4); EQX_CASE(5);
         default: return cudaErrorInvalidValue;
@@ -555,6 +637,7 @@ struct McFyParams {
     uint32_t m[MC_MAX_STEPS];                 // n_live - i of deal step i
     uint32_t thr[(MC_MAX_STEPS + 2) / 3];     // 2^32 mod (product of the m[i] of the steps word w serves)
     uint32_t rk0[10], rk1[10];                // Philox round keys: seed_lo + r * W0, seed_hi + r * W1
+    PotParams pots;                           // EV variant only (kernel seat order)
 };
 
 template <int NR> struct McShape {
@@ -576,7 +659,7 @@ __device__ __forceinline__ void philox_block(uint32_t c0, uint32_t c1, uint32_t 
 
 // NFX = fixed seats compiled in: MAX_SEATS - NR in general, 1 for the tables with at most one fixed seat (their
 // showdown then has NR + 1 slots instead of nine)
-template <int NR, int MC_THREADS, int NFX>
+template <int NR, int MC_THREADS, int NFX, bool EV>
 __global__ void __launch_bounds__(MC_THREADS, 1)
 equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__restrict__ g_blob,
                     const CardKey *__restrict__ g_card, long long *__restrict__ d_counts) {
@@ -590,7 +673,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
     unsigned char *srep_b = smem_raw + 13 * MC_T4;                                           // [64 cards][16 lanes] x 8 B
     uint2 *srep = reinterpret_cast<uint2 *>(srep_b);
     HashBlob *H = reinterpret_cast<HashBlob *>(srep_b + 64 * MC_REP * sizeof(uint2));
-    unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words + the mbarrier
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(H + 1);                // 19 words, the mbarrier, 9 chip sums
     BulkStage stage;
     stage.start(sred + 19, H, g_blob, (uint32_t)sizeof(HashBlob));
     for (int i = threadIdx.x; i < 64 * MC_REP; i += blockDim.x) {
@@ -599,6 +682,7 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         srep[i] = make_uint2(k.rk, k.sn | ((r >= 2 && r <= 14) ? 1u << (16 + r - 2) : 0u));
     }
     if (threadIdx.x < 19) sred[threadIdx.x] = 0ull;
+    if (EV && threadIdx.x < MAX_SEATS) sred[20 + threadIdx.x] = 0ull;
     stage.wait();
     const uint32_t tbl = staged_table_base(H);
 
@@ -616,6 +700,9 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 #pragma unroll
     for (int s = 0; s < NSLOT; s++) acc[s] = 0;
     uint32_t units = 0;
+    uint32_t chips[EV && NSLOT > 0 ? NSLOT : 1], since = 0;
+#pragma unroll
+    for (int s = 0; s < (EV ? NSLOT : 1); s++) chips[s] = 0;
 
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t tr = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; tr < prm.count; tr += nthreads) {
@@ -707,7 +794,12 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
 #pragma unroll
         for (int s = 0; s < NSLOT; s++) if (s < NR || s - NR < nf) acc[s] += at[s] * inc;
         units++;
+        if constexpr (EV && NSLOT > 0) {
+            pots_settle<NSLOT>(prm.pots, key, chips);
+            if (++since == prm.pots.flush_every) { chips_fold_thread<NSLOT>(chips, sred + 20); since = 0; }
+        }
     }
+    if constexpr (EV && NSLOT > 0) chips_fold_warp<NSLOT>(chips, sred + 20);
 
     // per-thread 16-bit halves (the launcher keeps a thread below 65536 trials) -> warp -> block -> global
     const int lane = threadIdx.x & 31, n_seats = NR + nf;
@@ -726,10 +818,11 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         if (w) atomicAdd(&o[os], w);
         if (e - w) atomicAdd(&o[9 + os], e - w);
         if (n - e) atomicAdd(&o[18 + os], n - e);
+        if (EV && sred[20 + s]) atomicAdd(&o[27 + os], sred[20 + s]);
     }
 }
 
-static size_t mc_smem(int threads) { return 13 * 4 * (size_t)(threads <= 512 ? 512 : 1024) + 64 * MC_REP * sizeof(uint2) + sizeof(HashBlob) + 20 * sizeof(unsigned long long); }
+static size_t mc_smem(int threads) { return 13 * 4 * (size_t)(threads <= 512 ? 512 : 1024) + 64 * MC_REP * sizeof(uint2) + sizeof(HashBlob) + 32 * sizeof(unsigned long long); }
 // threads per block by number of random seats: tables of up to three random seats fit 64 registers and run 1024
 // threads, the others 768 x 80 registers.  MCP_K4_THREADS=512|768|1024 overrides (A/B knob of tools/k4_ab.py; 1024 only
 // where the variant exists).
@@ -740,9 +833,9 @@ static int mc_threads(int nr) {
     return nr <= 3 ? 1024 : 768;
 }
 
-template <int NR, int MC_THREADS, int NFX>
+template <int NR, int MC_THREADS, int NFX, bool EV = false>
 static cudaError_t launch_mc_nfx(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
-    auto kern = equity_mc_fy_kernel<NR, MC_THREADS, NFX>;
+    auto kern = equity_mc_fy_kernel<NR, MC_THREADS, NFX, EV>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mc_smem(MC_THREADS));
     if (e != cudaSuccess) return e;
     kern<<<grid, MC_THREADS, mc_smem(MC_THREADS), st>>>(prm, tb.d_blob, tb.d_card, d_counts);
@@ -757,8 +850,17 @@ static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long
     return launch_mc_nfx<NR, MC_THREADS, NF_ALL>(prm, tb, d_counts, grid, st);
 }
 
+// EV variant: the general seat shape only, one block size per number of random seats (the nine chip accumulators cost
+// registers: 96 x 640 threads where the plain kernel runs 80 x 768; up to three random seats 80 x 768 instead of 64 x 1024)
+template <int NR> constexpr int mc_ev_threads() { return NR <= 3 ? 768 : 640; }
+template <int NR>
+static cudaError_t launch_mc_ev(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
+    return launch_mc_nfx<NR, mc_ev_threads<NR>(), MAX_SEATS - NR, true>(prm, tb, d_counts, grid, st);
+}
+
 cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
-                                long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+                                long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st,
+                                const PotArgs *pots) {
     if (n_trials == 0) return cudaSuccess;
     McFyParams prm;
     memset(&prm, 0, sizeof prm);
@@ -785,13 +887,32 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
             if (i < 2 * nr || i - 2 * nr < prm.n_board) prod *= prm.m[i];
         prm.thr[w] = (uint32_t)((1ull << 32) % prod);
     }
+    const bool ev = pots && pots->n_pots > 0;
+    make_pot_params(ev ? pots : nullptr, prm.seat_of, a.n_seats, &prm.pots);
     const int grid = di.sm_count;
-    const int MC_THREADS = mc_threads(nr);
+    const int MC_THREADS = ev ? (nr <= 3 ? 768 : 640) : mc_threads(nr);
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
     for (uint64_t done = 0; done < n_trials; done += per_launch) {
         prm.first = first_trial + done;
         prm.count = (n_trials - done) < per_launch ? (n_trials - done) : per_launch;
         cudaError_t e;
+        if (ev) {
+            switch (nr) {
+                case 0: e = launch_mc_ev<0>(prm, tb, d_counts, grid, st); break;
+                case 1: e = launch_mc_ev<1>(prm, tb, d_counts, grid, st); break;
+                case 2: e = launch_mc_ev<2>(prm, tb, d_counts, grid, st); break;
+                case 3: e = launch_mc_ev<3>(prm, tb, d_counts, grid, st); break;
+                case 4: e = launch_mc_ev<4>(prm, tb, d_counts, grid, st); break;
+                case 5: e = launch_mc_ev<5>(prm, tb, d_counts, grid, st); break;
+                case 6: e = launch_mc_ev<6>(prm, tb, d_counts, grid, st); break;
+                case 7: e = launch_mc_ev<7>(prm, tb, d_counts, grid, st); break;
+                case 8: e = launch_mc_ev<8>(prm, tb, d_counts, grid, st); break;
+                case 9: e = launch_mc_ev<9>(prm, tb, d_counts, grid, st); break;
+                default: return cudaErrorInvalidValue;
+            }
+            if (e != cudaSuccess) return e;
+            continue;
+        }
         switch (nr) {
             case 0: e = MC_THREADS == 1024 ? launch_mc<0, 1024>(prm, tb, d_counts, grid, st) : MC_THREADS == 768 ? launch_mc<0, 768>(prm, tb, d_counts, grid, st) : launch_mc<0, 512>(prm, tb, d_counts, grid, st); break;
             case 1: e = MC_THREADS == 1024 ? launch_mc<1, 1024>(prm, tb, d_counts, grid, st) : MC_THREADS == 768 ? launch_mc<1, 768>(prm, tb, d_counts, grid, st) : launch_mc<1, 512>(prm, tb, d_counts, grid, st); break;

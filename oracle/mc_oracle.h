@@ -87,7 +87,7 @@ uint32_t orc_eval_mask(uint64_t mask);                                 /* direct
 uint32_t orc_eval_mask_literal(uint64_t mask, int *would_throw);       /* literal path on cards in ascending bit order */
 void     orc_eval_batch(const uint64_t *masks, size_t n, uint32_t *keys, int which /*0 direct,1 best-of-subsets,2 literal*/, int threads);
 
-/* exhaustive enumeration of all C(52,k) hands, k = 5,6,7, in card-id lexicographic order.
+/* exhaustive enumeration of all C(52,k) hands, k = 5,6,7, in colex order of card ids (index = sum_i C(c_i, i+1)).
  * which: 0 direct bitmask, 1 rank-count best-of-subsets.  hist[cat], key_sum, n_distinct may be NULL.
  * first/count select a sub-range of combination indices (count = 0 -> to the end). */
 int  orc_enumerate(int k, int which, int threads, uint64_t first, uint64_t count,
@@ -100,6 +100,12 @@ uint64_t orc_enumerate_crosscheck(int k, int threads);
 int  orc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
                            int threads, int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_boards);
 
+/* EV: the same enumeration, each board settled by group-winners (gameplay.clj:118-120) + the literal
+ * update-stacks (:104-116, orc_update_stacks); chips[seat] = sum over the boards of what the seat receives */
+int  orc_equity_exhaustive_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask, int threads,
+                              const long long *pot_bet, const int *pot_n, const unsigned *pot_players, int n_pots,
+                              int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips, uint64_t *n_boards);
+
 /* Philox4x32-10 and the deal spec shared with the CUDA kernels (DESIGN.md "Deal spec") */
 void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]);
 uint64_t orc_random_hand_mask(uint64_t seed, uint64_t index, int n_cards);   /* cfg-1 hands */
@@ -109,6 +115,11 @@ int  orc_deal_trial(const uint64_t *hole_masks, int n_seats, uint64_t board_mask
 int  orc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
                    uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
                    int64_t *win, int64_t *tie, int64_t *loss);
+
+int  orc_equity_mc_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                      uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
+                      const long long *pot_bet, const int *pot_n, const unsigned *pot_players, int n_pots,
+                      int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips);
 
 /* one cell of the 169x169 preflop matrix (class ids: see include/mcpoker.h) by brute force */
 int  orc_preflop_cell(int class_a, int class_b, int threads, int64_t wtl[3]);

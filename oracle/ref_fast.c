@@ -312,9 +312,28 @@ static void count_showdown(const uint32_t *keys, int n, int64_t *win, int64_t *t
     }
 }
 
-int orc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
-                          int threads, int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_boards) {
+/* EV: the reference's settlement of one showdown -- group-winners gameplay.clj:118-120 on the keys, then the
+ * literal update-stacks :104-116 (ref_literal.c) over the pots; chips[seat] += what the seat receives. */
+typedef struct { const long long *bet; const int *n; const unsigned *players; int n_pots; } pots_t;
+static int settle_showdown(const uint32_t *keys, int n_seats, const pots_t *P, long long *chips /* 32 seats */) {
+    int group_of[9];
+    const int ng = orc_group_winners(keys, n_seats, group_of);
+    unsigned sets[9] = {0};
+    for (int s = 0; s < n_seats; s++) sets[group_of[s]] |= 1u << s;
+    return orc_update_stacks(sets, ng, P->bet, P->n, P->players, P->n_pots, chips);
+}
+static int check_pots(const pots_t *P, int n_seats) {
+    if (P->n_pots < 1) return -1;
+    for (int p = 0; p < P->n_pots; p++)
+        if (P->players[p] == 0 || (P->players[p] >> n_seats) || P->bet[p] < 0 || P->n[p] < 0) return -1;
+    return 0;
+}
+
+static int equity_exhaustive_impl(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                                  int threads, const pots_t *P, int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips,
+                                  uint64_t *n_boards) {
     if (n_seats < 1 || n_seats > 9) return -1;
+    if (P && check_pots(P, n_seats)) return -1;
     binom_init();
     uint64_t used = board_mask | dead_mask;
     if (board_mask & ~DECK_MASK) return -1;
@@ -332,10 +351,12 @@ int orc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t boar
     uint64_t total = BINOM[nd][k];
     int nt = use_threads(threads);
     int64_t W[9] = {0}, T[9] = {0}, L[9] = {0};
+    long long CH[32] = {0};
     uint64_t chunk = (total + (uint64_t)nt - 1) / (uint64_t)nt;
 #pragma omp parallel num_threads(nt)
     {
         int64_t w[9] = {0}, t_[9] = {0}, l[9] = {0};
+        long long ch[32] = {0};
 #pragma omp for schedule(static, 1)
         for (int t = 0; t < nt; t++) {
             uint64_t lo = chunk * (uint64_t)t, hi = lo + chunk;
@@ -349,15 +370,26 @@ int orc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t boar
                 uint32_t keys[9];
                 for (int s = 0; s < n_seats; s++) keys[s] = orc_eval_mask(b | hole_masks[s]);
                 count_showdown(keys, n_seats, w, t_, l);
+                if (P) settle_showdown(keys, n_seats, P, ch);
                 if (k > 0) colex_next(c, k, nd);
             }
         }
 #pragma omp critical
-        { for (int s = 0; s < 9; s++) { W[s] += w[s]; T[s] += t_[s]; L[s] += l[s]; } }
+        { for (int s = 0; s < 9; s++) { W[s] += w[s]; T[s] += t_[s]; L[s] += l[s]; CH[s] += ch[s]; } }
     }
-    for (int s = 0; s < n_seats; s++) { win[s] = W[s]; tie[s] = T[s]; loss[s] = L[s]; }
+    for (int s = 0; s < n_seats; s++) { win[s] = W[s]; tie[s] = T[s]; loss[s] = L[s]; if (chips) chips[s] = CH[s]; }
     if (n_boards) *n_boards = total;
     return 0;
+}
+int orc_equity_exhaustive(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                          int threads, int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_boards) {
+    return equity_exhaustive_impl(hole_masks, n_seats, board_mask, dead_mask, threads, 0, win, tie, loss, 0, n_boards);
+}
+int orc_equity_exhaustive_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask, int threads,
+                             const long long *pot_bet, const int *pot_n, const unsigned *pot_players, int n_pots,
+                             int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips, uint64_t *n_boards) {
+    const pots_t P = {pot_bet, pot_n, pot_players, n_pots};
+    return equity_exhaustive_impl(hole_masks, n_seats, board_mask, dead_mask, threads, &P, win, tie, loss, chips, n_boards);
 }
 
 /* ---------------------------------------------------------------------------------------------- */
@@ -474,28 +506,44 @@ static int check_mc_args(const uint64_t *hole_masks, int n_seats, uint64_t board
     return 0;
 }
 
-int orc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
-                  uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
-                  int64_t *win, int64_t *tie, int64_t *loss) {
+static int equity_mc_impl(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                          uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads, const pots_t *P,
+                          int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips) {
     if (check_mc_args(hole_masks, n_seats, board_mask, dead_mask)) return -1;
+    if (P && check_pots(P, n_seats)) return -1;
     int nt = use_threads(threads);
     (void)nt;
     int64_t W[9] = {0}, T[9] = {0}, L[9] = {0};
+    long long CH[32] = {0};
 #pragma omp parallel num_threads(nt)
     {
         int64_t w[9] = {0}, t_[9] = {0}, l[9] = {0};
+        long long ch[32] = {0};
 #pragma omp for schedule(static)
         for (long long i = 0; i < (long long)n_trials; i++) {
             uint64_t holes[9], board; uint32_t keys[9];
             orc_deal_trial(hole_masks, n_seats, board_mask, dead_mask, seed, first_trial + (uint64_t)i, holes, &board);
             for (int s = 0; s < n_seats; s++) keys[s] = orc_eval_mask(board | holes[s]);
             count_showdown(keys, n_seats, w, t_, l);
+            if (P) settle_showdown(keys, n_seats, P, ch);
         }
 #pragma omp critical
-        { for (int s = 0; s < 9; s++) { W[s] += w[s]; T[s] += t_[s]; L[s] += l[s]; } }
+        { for (int s = 0; s < 9; s++) { W[s] += w[s]; T[s] += t_[s]; L[s] += l[s]; CH[s] += ch[s]; } }
     }
-    for (int s = 0; s < n_seats; s++) { win[s] = W[s]; tie[s] = T[s]; loss[s] = L[s]; }
+    for (int s = 0; s < n_seats; s++) { win[s] = W[s]; tie[s] = T[s]; loss[s] = L[s]; if (chips) chips[s] = CH[s]; }
     return 0;
+}
+int orc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                  uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
+                  int64_t *win, int64_t *tie, int64_t *loss) {
+    return equity_mc_impl(hole_masks, n_seats, board_mask, dead_mask, seed, first_trial, n_trials, threads, 0, win, tie, loss, 0);
+}
+int orc_equity_mc_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                     uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
+                     const long long *pot_bet, const int *pot_n, const unsigned *pot_players, int n_pots,
+                     int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips) {
+    const pots_t P = {pot_bet, pot_n, pot_players, n_pots};
+    return equity_mc_impl(hole_masks, n_seats, board_mask, dead_mask, seed, first_trial, n_trials, threads, &P, win, tie, loss, chips);
 }
 
 /* ---------------------------------------------------------------------------------------------- */

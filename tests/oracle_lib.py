@@ -160,6 +160,40 @@ def equity_mc(holes, board, dead, seed, first, n_trials, threads=0):
     return rc, list(w), list(t), list(l)
 
 
+def _pots(pots):
+    k = len(pots)
+    return ((C.c_longlong * max(k, 1))(*[p[0] for p in pots]), (C.c_int * max(k, 1))(*[p[1] for p in pots]),
+            (C.c_uint * max(k, 1))(*[sum(1 << s for s in p[2]) for p in pots]), k)
+
+
+def equity_exhaustive_ev(holes, pots, board=0, dead=0, threads=0):
+    """pots = [(bet, n, [seats])] -> (rc, win, tie, loss, chips, n_boards)"""
+    n = len(holes)
+    h = (C.c_uint64 * n)(*holes)
+    w, t, l, ch = (C.c_int64 * n)(), (C.c_int64 * n)(), (C.c_int64 * n)(), (C.c_int64 * n)()
+    nb = C.c_uint64(0)
+    bet, cnt, msk, k = _pots(pots)
+    L = lib()
+    L.orc_equity_exhaustive_ev.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_longlong),
+                                           C.POINTER(C.c_int), C.POINTER(C.c_uint), C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                           C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]
+    rc = L.orc_equity_exhaustive_ev(h, n, board, dead, threads, bet, cnt, msk, k, w, t, l, ch, C.byref(nb))
+    return rc, list(w), list(t), list(l), list(ch), nb.value
+
+
+def equity_mc_ev(holes, pots, board, dead, seed, first, n_trials, threads=0):
+    n = len(holes)
+    h = (C.c_uint64 * n)(*holes)
+    w, t, l, ch = (C.c_int64 * n)(), (C.c_int64 * n)(), (C.c_int64 * n)(), (C.c_int64 * n)()
+    bet, cnt, msk, k = _pots(pots)
+    L = lib()
+    L.orc_equity_mc_ev.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int,
+                                   C.POINTER(C.c_longlong), C.POINTER(C.c_int), C.POINTER(C.c_uint), C.c_int, C.POINTER(C.c_int64),
+                                   C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    rc = L.orc_equity_mc_ev(h, n, board, dead, seed, first, n_trials, threads, bet, cnt, msk, k, w, t, l, ch)
+    return rc, list(w), list(t), list(l), list(ch)
+
+
 def philox(ctr, key):
     c, k, o = (C.c_uint32 * 4)(*ctr), (C.c_uint32 * 2)(*key), (C.c_uint32 * 4)()
     lib().orc_philox4x32_10(c, k, o)

@@ -539,6 +539,80 @@ def test_end_game_one_call(gpu, oracle):
         assert winners == sets[0]
 
 
+def _random_pots(rng, n_seats, big=False):
+    pots = []
+    for _ in range(rng.randint(1, 8 if not big else 3)):
+        players = rng.sample(range(n_seats), rng.randint(1, n_seats))
+        if big:
+            pots.append((rng.randint(1, 2 ** 26), rng.randint(1, 9), players))
+        else:
+            pots.append((rng.randint(0, 400), rng.randint(0, n_seats), players))
+    return pots
+
+
+def test_equity_ev_exhaustive_vs_oracle(gpu, oracle):
+    """chips per seat under update-stacks (gameplay.clj:104-116) summed over every board, bit-exact against
+    the oracle (group-winners + the literal update-stacks per board); counts equal to the plain call"""
+    rng = random.Random(23)
+    api = gpu.api
+    for n_seats, n_board, n_dead, big in [(2, 0, 0, False), (2, 3, 0, True), (3, 3, 2, False), (9, 3, 0, False), (4, 4, 1, True),
+                                          (6, 5, 0, False), (3, 2, 0, False), (5, 4, 0, False), (9, 4, 0, True)]:
+        ids = rng.sample(range(52), 2 * n_seats + n_board + n_dead)
+        holes = [api.mask_of_ids(ids[2 * s:2 * s + 2]) for s in range(n_seats)]
+        board = api.mask_of_ids(ids[2 * n_seats:2 * n_seats + n_board])
+        dead = api.mask_of_ids(ids[2 * n_seats + n_board:])
+        pots = _random_pots(rng, n_seats, big)
+        w, t, l, chips, nb = api.equity_exhaustive_ev(holes, pots, board, dead)
+        rc, wo, to, lo, co, nbo = oracle.equity_exhaustive_ev(holes, pots, board, dead)
+        assert rc == 0 and (w, t, l, chips, nb) == (wo, to, lo, co, nbo), (n_seats, n_board, pots)
+        assert (w, t, l, nb) == api.equity_exhaustive(holes, board, dead)
+    # AA vs KK, main pot 2 x 10 and a side pot only KK plays for: by hand from the golden counts
+    holes = [api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50])]
+    w, t, l, chips, nb = api.equity_exhaustive_ev(holes, [(10, 2, [0, 1]), (5, 1, [1])])
+    assert chips == [20 * 1388072 + 10 * 6056, 20 * 318176 + 10 * 6056 + 5 * 1712304]
+    E = gpu.engine
+    for bad in ([], [(10, 2, [])], [(10, 2, [2])], [(2 ** 30, 2, [0, 1])], [(1, 1, [0])] * 9, [(-1, 2, [0])]):
+        with pytest.raises(E.McError) as e:
+            api.equity_exhaustive_ev(holes, bad)
+        assert e.value.code == E.MC_ERR_INVALID
+
+
+def test_equity_ev_monte_carlo_vs_oracle(gpu, oracle):
+    """the same per Monte Carlo trial (K4's EV variant): every number of random seats, preflop to river, small and
+    huge pots (the huge ones force the per-thread chip accumulators to fold every few trials), bit-exact vs the oracle;
+    counts equal to the plain call's"""
+    rng = random.Random(29)
+    api = gpu.api
+    for n_seats in range(1, 10):
+        for n_fixed in sorted({0, 1, n_seats // 2, n_seats}):
+            n_known = rng.choice([0, 0, 3, 4, 5])
+            ids = rng.sample(range(52), 2 * n_fixed + n_known)
+            fixed_at = set(rng.sample(range(n_seats), n_fixed))
+            holes, k = [], 0
+            for s in range(n_seats):
+                if s in fixed_at:
+                    holes.append(api.mask_of_ids(ids[2 * k:2 * k + 2]))
+                    k += 1
+                else:
+                    holes.append(0)
+            board = api.mask_of_ids(ids[2 * n_fixed:])
+            pots = _random_pots(rng, n_seats, big=rng.random() < 0.3)
+            seed, first, n = rng.getrandbits(64), rng.getrandbits(40), 20_000
+            got = api.equity_mc_ev(holes, pots, board, 0, seed, first, n)
+            rc, w, t, l, ch = oracle.equity_mc_ev(holes, pots, board, 0, seed, first, n)
+            assert rc == 0 and got == (w, t, l, ch), (n_seats, n_fixed, n_known, pots)
+            assert got[:3] == api.equity_mc(holes, board, 0, seed, first, n)
+    # 9 seats, three nested pots, enough trials that every thread runs many: split invariance of the chip sums
+    holes = [api.mask_of_ids([12, 25])] + [0] * 8
+    pots = [(100, 9, list(range(9))), (250, 6, [0, 2, 3, 5, 6, 8]), (400, 3, [0, 3, 8])]
+    full = api.equity_mc_ev(holes, pots, 0, 0, SEED, 0, 1 << 21)
+    a = api.equity_mc_ev(holes, pots, 0, 0, SEED, 0, 700_001)
+    b = api.equity_mc_ev(holes, pots, 0, 0, SEED, 700_001, (1 << 21) - 700_001)
+    assert all([x + y for x, y in zip(a[k], b[k])] == full[k] for k in range(4))
+    rc, w, t, l, ch = oracle.equity_mc_ev(holes, pots, 0, 0, SEED, 0, 1 << 18)
+    assert api.equity_mc_ev(holes, pots, 0, 0, SEED, 0, 1 << 18) == (w, t, l, ch)
+
+
 def test_lifecycle_is_safe_against_calls_in_flight(gpu, oracle):
     """the header's promise: mc_init* / mc_shutdown wait for calls in flight and calls never run on a context that is
     being torn down.  Four threads hammer compute calls (batch, single-hand ticket path, equity) while a fifth cycles

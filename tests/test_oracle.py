@@ -249,3 +249,21 @@ def test_preflop_cell_aa_kk(oracle):
     assert oracle.lib().orc_preflop_cell(168, 154, 0, wtl) == 0
     g = SG["cell_AA_KK"]
     assert list(wtl) == [g["win"], g["tie"], g["loss"]]
+
+
+def test_ev_settlement_conserves_chips_when_shares_divide(oracle):
+    """oracle EV (group-winners + literal update-stacks per board): with one pot everybody plays for and a total every
+    possible split divides, every board pays out the whole pot; AA vs KK by hand from the golden counts"""
+    aa, kk = oracle.card_bit(12) | oracle.card_bit(25), oracle.card_bit(37) | oracle.card_bit(50)
+    rc, w, t, l, ch, nb = oracle.equity_exhaustive_ev([aa, kk], [(10, 2, [0, 1]), (5, 1, [1])])
+    assert rc == 0 and nb == 1712304
+    assert ch == [20 * 1388072 + 10 * 6056, 20 * 318176 + 10 * 6056 + 5 * 1712304]
+    third = oracle.card_bit(0) | oracle.card_bit(14)
+    board = oracle.card_bit(5) | oracle.card_bit(19) | oracle.card_bit(33)
+    rc, w, t, l, ch, nb = oracle.equity_exhaustive_ev([aa, kk, third], [(2, 3, [0, 1, 2])], board)      # total 6: splits 1, 2, 3 ways
+    assert rc == 0 and sum(ch) == 6 * nb
+    rc, w, t, l, ch = oracle.equity_mc_ev([aa, 0, 0], [(2, 3, [0, 1, 2])], 0, 0, 9, 0, 5000)
+    assert rc == 0 and sum(ch) == 6 * 5000
+    rc, w2, t2, l2 = oracle.equity_mc([aa, 0, 0], 0, 0, 9, 0, 5000)
+    assert (w, t, l) == (w2, t2, l2)
+    assert oracle.equity_exhaustive_ev([aa, kk], [(10, 2, [])])[0] == -1           # a pot nobody plays for: the reference divides by zero
