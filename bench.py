@@ -38,6 +38,21 @@ OPS = {"eval": 46, "enum": 62, "board2": 69, "mc9": 612}
 # entries, 18 hash loads, flush -- plus 45 from the random D / V addresses of a warp sharing banks)
 MC9_SMEM_WAVEFRONTS_PER_32_TRIALS = 186
 METRIC = "7-card evals/s"
+# SHA-256 of the 27 config-4 counts ("w0,..,w8,t0,..,l8") by log2(trials), recorded from a 1-GPU run of this bench
+# (seed 0x5EED5EED, seat 0 = A-A, eight random seats): any number of ranks must reproduce them
+MC9_COUNTS_SHA256 = {}
+
+
+K1_SOURCES = ("kernels.cu", "hashtab.cuh", "hashtab_build.h", "common.cuh", "eval.cuh")
+
+
+def k1_source_hash():
+    """SHA-256 of the sources the K1 kernel and its table images are built from (ties roofline.traffic to a capture)"""
+    import hashlib
+    h = hashlib.sha256()
+    for f in K1_SOURCES:
+        h.update(open(os.path.join(ROOT, "monte-carlo_b200", "csrc", f), "rb").read())
+    return h.hexdigest()
 
 
 def load_peaks():
@@ -233,9 +248,14 @@ def run_ours(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    first_call = {}                              # one-time costs a caller pays once per process (reported, never timed as work)
+    t0 = time.perf_counter()
     E.init(devices=[local])
+    first_call["mc_init_s"] = time.perf_counter() - t0
+    first_call["mc_init_note"] = "CUDA context + evaluation of the table representatives on the GPU + hash-and-displace searches on the host + upload"
     L = E.lib()
     stream = torch.cuda.current_stream().cuda_stream
+    sharding = pkg.sharding
     hbm_peak, sm_max_mhz, peak_src = load_peaks()
     sms = torch.cuda.get_device_properties(local).multi_processor_count
 
@@ -284,6 +304,28 @@ def run_ours(args):
                       ("nibble_rankset_table_v2", E.KEY_NIBBLE_TABLE), ("nibble_plane_hash_v5", E.KEY_NIBBLE_HASH)):
         v_ms = timed_region(torch, dist, world, lambda: k1_step(fmt), max(2, args.steps // 2), 1)
         variants[name] = world * n * max(2, args.steps // 2) / (v_ms * 1e-3)
+
+    # ---- K1 on flop / turn hands (player->hand-value on 5 and 6 cards, hand_evaluator.clj:171): the same
+    # kernel on its flop / turn table image, 8 B in + 4 B out per hand, against the same HBM roofline
+    k1_stages = {}
+    for n_cards, name in ((5, "k1_flop_5card"), (6, "k1_turn_6card")):
+        E.check(L.mc_random_hands_dev(SEED + n_cards, rank * n, n, n_cards, masks.data_ptr(), stream))
+
+        def stage_step():
+            E.check(L.mc_eval_batch_dev(masks.data_ptr(), n, keys.data_ptr(), E.KEY_NIBBLE, n_cards, stream))
+        st_steps = max(4, args.steps // 2)
+        st_ms = timed_region(torch, dist, world, stage_step, st_steps, 3)
+        if rank == 0:
+            import oracle_lib as oracle
+            got = keys[:check_n].cpu().numpy().view(np.uint32)
+            if not np.array_equal(got, oracle.eval_batch(oracle.random_hands(SEED + n_cards, 0, check_n, n_cards), 0)):
+                raise SystemExit("K1 %d-card keys differ from the oracle" % n_cards)
+        gbs = n * ALGO_BYTES_PER_EVAL / (st_ms / st_steps * 1e-3) / 1e9
+        k1_stages[name] = {"evals_per_s": world * n * st_steps / (st_ms * 1e-3), "ms": st_ms / st_steps, "hands_per_gpu": n,
+                           "parity_checked": True if rank == 0 else None,
+                           "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
+                                        "kernel": "eval_stream_hash_kernel<6, Lay56, uint32_t>"}}
+    E.check(L.mc_random_hands_dev(SEED, rank * n, n, 7, masks.data_ptr(), stream))       # back to the river hands for e2e
 
     # ---- e2e: the host-buffer C-ABI calls, pinned memory, H2D + kernels + D2H inside the timed region ----
     # Three wire formats of the same batch call, all bound by the host link:
@@ -384,13 +426,13 @@ def run_ours(args):
             pipes = {"error": str(ex)}
 
     # ---- other BASELINE configs --------------------------------------------------------------------
-    work = {}
+    work = dict(k1_stages)
     f_sm = (clocks.get("sm_mhz") or sm_max_mhz) * 1e6
     int_peak = sms * 128 * f_sm                                 # thread-level int ops/s at the measured clock
 
     out = torch.zeros(16, dtype=torch.int64, device="cuda")
     total7 = 133784560
-    lo7, hi7 = total7 * rank // world, total7 * (rank + 1) // world
+    lo7, hi7 = sharding.shard_range(total7, rank, world)
 
     def enum_step():
         out.zero_()
@@ -410,27 +452,30 @@ def run_ours(args):
     cnt = torch.zeros(27, dtype=torch.int64, device="cuda")
     holes2 = (C.c_uint64 * 2)(api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50]))
     nb = 1712304
-    lob, hib = nb * rank // world, nb * (rank + 1) // world
 
-    def eqx_step():
+    def eqx_step():        # 18 us of work: NOT sharded (an all-reduce costs more than the job); every rank runs the whole job
         cnt.zero_()
-        E.check(L.mc_equity_exhaustive_dev(holes2, 2, 0, 0, lob, hib - lob, cnt.data_ptr(), stream))
-        if world > 1:
-            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        E.check(L.mc_equity_exhaustive_dev(holes2, 2, 0, 0, 0, nb, cnt.data_ptr(), stream))
 
     ms3 = timed_region(torch, dist, world, eqx_step, 20, 3)
     c3 = cnt.cpu().tolist()
     rate3 = nb * 20 / (ms3 * 1e-3)
+
+    def eqx_back_to_back():
+        E.check(L.mc_equity_exhaustive_dev(holes2, 2, 0, 0, 0, nb, cnt.data_ptr(), stream))
+    ms3b = timed_region(torch, dist, world, eqx_back_to_back, 200, 5)
     work["config3_aa_vs_kk_exhaustive"] = {
-        "boards_per_s": rate3, "ms": ms3 / 20, "counts_equal_golden": [c3[0], c3[1], c3[9]] == [1388072, 318176, 6056],
+        "boards_per_s": rate3, "ms": ms3 / 20, "us_per_launch_back_to_back": 1e3 * ms3b / 200,
+        "counts_equal_golden": [c3[0], c3[1], c3[9]] == [1388072, 318176, 6056],
+        "sharding": "none: every rank runs the whole 1.7 M-board job (replicas); it is too short to split",
         "roofline": {"bound": "int_issue", "ops_per_unit": OPS["board2"], "achieved": rate3 * OPS["board2"] / 1e12,
-                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate3 * OPS["board2"] / (world * int_peak),
+                     "peak": int_peak / 1e12, "unit": "Tint-op/s", "frac": rate3 * OPS["board2"] / int_peak,
                      "note": "microseconds of work: launch-bound"}}
 
     holes9 = (C.c_uint64 * 9)(api.mask_of_ids([12, 25]), 0, 0, 0, 0, 0, 0, 0, 0)
 
     def mc_run(total_trials):
-        lo, hi = total_trials * rank // world, total_trials * (rank + 1) // world
+        lo, hi = sharding.shard_range(total_trials, rank, world)
         cnt.zero_()
         E.check(L.mc_equity_mc_dev(holes9, 9, 0, 0, SEED, lo, hi - lo, cnt.data_ptr(), stream))
         if world > 1:
@@ -456,7 +501,7 @@ def run_ours(args):
     # the same workload through the host-buffer call a JVM makes (mc_equity_mc: hole masks in, 27 host counts out,
     # wall clock around the call): inputs and outputs are a few hundred bytes, so end to end = the device rate
     e2e4_log2 = min(mc_log2, 32)
-    lo4, hi4 = (1 << e2e4_log2) * rank // world, (1 << e2e4_log2) * (rank + 1) // world
+    lo4, hi4 = sharding.shard_range(1 << e2e4_log2, rank, world)
     got4 = [None]
 
     def mc_host_call():
@@ -467,7 +512,35 @@ def run_ours(args):
     ms4_host = wall_region(torch, dist, world, mc_host_call, 1, 1)
     g4 = got4[0].cpu().tolist()
     assert all(g4[s] + g4[9 + s] + g4[18 + s] == 1 << e2e4_log2 for s in range(9)), "mc_equity_mc counts do not add up"
+    # G-invariance on the driver's run: trial t depends only on (seed, t), so the 27 counts of 2^34 trials must be the
+    # same whatever the number of ranks; their SHA-256 is compared with the value recorded from a 1-GPU run
+    import hashlib
+    counts_sha = hashlib.sha256(",".join(str(v) for v in c4).encode()).hexdigest()
+    golden_sha = MC9_COUNTS_SHA256.get(mc_log2)
+    if rank == 0 and golden_sha and counts_sha != golden_sha:
+        raise SystemExit("config 4: the 27 counts differ from the 1-GPU golden for 2^%d trials" % mc_log2)
+    # EV variant: the same table with three side pots settled per trial (update-stacks gameplay.clj:104-116)
+    cnt36 = torch.zeros(36, dtype=torch.int64, device="cuda")
+    pots = [(100, 9, list(range(9))), (250, 6, [0, 2, 3, 5, 6, 8]), (400, 3, [0, 3, 8])]
+    p_bet = (C.c_int64 * 3)(*[p[0] for p in pots]); p_n = (C.c_int32 * 3)(*[p[1] for p in pots])
+    p_msk = (C.c_uint32 * 3)(*[sum(1 << q for q in p[2]) for p in pots])
+    ev_trials = 1 << min(mc_log2, 32)
+
+    def mc_ev_run():
+        lo, hi = sharding.shard_range(ev_trials, rank, world)
+        cnt36.zero_()
+        E.check(L.mc_equity_mc_ev_dev(holes9, 9, 0, 0, SEED, lo, hi - lo, p_bet, p_n, p_msk, 3, cnt36.data_ptr(), stream))
+        if world > 1:
+            dist.all_reduce(cnt36, op=dist.ReduceOp.SUM)
+    ms4ev = timed_region(torch, dist, world, mc_ev_run, 1, 1)
+    c4ev = cnt36.cpu().tolist()
+    work["config4_mc_9_seats_ev_3_pots"] = {
+        "trials_per_s": ev_trials / (ms4ev * 1e-3), "trials": ev_trials, "ms": ms4ev, "pots": "9 x 100, 6 x 250, 3 x 400 chips (nested)",
+        "seat0_chips_per_trial": c4ev[27] / ev_trials, "chips_paid_per_trial": sum(c4ev[27:36]) / ev_trials,
+        "frac_of_plain_kernel": ev_trials / (ms4ev * 1e-3) / rate4,
+        "note": "K4 EV variant: 640 threads x 96 registers (nine chip accumulators) against 768 x 80 of the plain kernel"}
     work["config4_mc_9_seats"] = {
+        "counts_sha256": counts_sha, "counts_equal_1gpu_golden": (counts_sha == golden_sha) if golden_sha else None,
         "trials_per_s": rate4, "evals_per_s": 9 * rate4, "trials": trials, "log2_trials": mc_log2, "ms": ms4,
         "seat0_equity": (c4[0] + c4[9] / 2) / trials, "counts_sum_ok": all(c4[s] + c4[9 + s] + c4[18 + s] == trials for s in range(9)),
         "collective": "one NCCL all_reduce(int64 x 27)" if world > 1 else "none (1 rank)",
@@ -505,8 +578,11 @@ def run_ours(args):
 
     # config 5: the 169 x 169 preflop matrix, suit-canonical matchups dealt round-robin over the ranks, one all-reduce
     if not args.no_matrix:
+        t0 = time.perf_counter()
         api.preflop_matrix_part(rank, world)                      # warm-up: builds and caches the matchup list
         torch.cuda.synchronize()
+        first_call["first_mc_preflop_matrix_part_s"] = time.perf_counter() - t0
+        first_call["first_mc_preflop_matrix_part_note"] = "includes the one-time suit-canonical matchup list (812,175 pairs x 24 permutations on the host)"
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
@@ -533,8 +609,11 @@ def run_ours(args):
                          "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": boards5 / s5 * OPS["board2"] / (world * int_peak)}}
 
         # the same matrix by boards: canonical boards dealt round-robin over the ranks, all-reduce of the wins
+        t0 = time.perf_counter()
         api.preflop_wins_by_boards(rank, world)                   # warm-up: builds and caches the canonical board list
         torch.cuda.synchronize()
+        first_call["first_mc_preflop_wins_by_boards_s"] = time.perf_counter() - t0
+        first_call["first_mc_preflop_wins_by_boards_note"] = "includes the one-time enumeration of the 134,459 suit-canonical boards on the host"
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
@@ -569,11 +648,17 @@ def run_ours(args):
                "fast_bitmask_oracle_evals_per_s": fast_n / (time.perf_counter() - t0)}
 
     if rank == 0:
-        traffic = None
+        # dram bytes per launch from the ncu --set full capture of THIS kernel source (tools/k1_traffic.py records the hash
+        # of the K1 sources beside the counters); a capture of other sources is not reported
+        traffic, traffic_note = None, "no capture (profiles/k1_traffic.json)"
         tp = os.path.join(ROOT, "profiles", "k1_traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get("dram_bytes_per_launch_at_bench_size")
+                tj = json.load(open(tp))
+                if tj.get("k1_source_sha256") == k1_source_hash() and args.batch_log2 == tj.get("batch_log2", 28):
+                    traffic, traffic_note = tj.get("dram_bytes_per_launch_at_bench_size"), "ncu capture of these K1 sources: " + tj.get("source", "")
+                else:
+                    traffic_note = "the K1 sources (or the batch size) changed since the ncu capture in profiles/k1_traffic.json: not reported"
             except Exception:
                 traffic = None
         line = {
@@ -585,8 +670,8 @@ def run_ours(args):
                        "hands_per_gpu_per_step": n, "l2": "inputs (2 GiB) + outputs (1 GiB) per step exceed the 126 MB L2",
                        "parallelism": "independent slices per rank, no data-path collective"},
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "eval7_stream_hash_kernel", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
+                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "traffic_source": traffic_note, "peak_source": peak_src,
+                         "kernel": "eval_stream_hash_kernel<6, Lay7, uint32_t>", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
                          "int_issue_frac": (value / world) * OPS["eval"] / int_peak, "ops_per_eval": OPS["eval"]},
             "e2e": {"value": e2e32_value, "unit": "evals/s", "h2d_bytes_per_step": 4 * ne, "d2h_bytes_per_step": 2 * ne,
                     "hands_per_step": ne,
@@ -598,7 +683,7 @@ def run_ours(args):
                                   "call": "mc_eval7_batch (8-byte masks in, 4-byte nibble keys out)"},
                     "link": link},
             "gpu_launches": gpu_launches, "clocks": clocks, "parity_checked": parity,
-            "k1_variants_evals_per_s": variants, "int_pipes_measured": pipes, "workloads": work,
+            "k1_variants_evals_per_s": variants, "int_pipes_measured": pipes, "first_call_costs": first_call, "workloads": work,
         }
         if cpu:
             line["cpu_baseline"] = cpu

@@ -126,9 +126,9 @@ def eval_batch(hands, in_format, key_format=E.KEY_NIBBLE, stage_cards=0):
     """any wire format in (IN_MASK64 uint64, IN_PACKED48 6 bytes, IN_COLEX32 uint32), keys (uint32) or class ids
     (uint16, KEY_CLASS16) out"""
     E.ensure_init()
-    dt, per = {E.IN_MASK64: (np.uint64, 1), E.IN_PACKED48: (np.uint8, 6), E.IN_COLEX32: (np.uint32, 1)}[in_format]
-    hands = np.ascontiguousarray(hands, dtype=dt)
-    n = hands.size // per
+    fmt = {E.IN_MASK64: (np.uint64, 1), E.IN_PACKED48: (np.uint8, 6), E.IN_COLEX32: (np.uint32, 1)}.get(in_format)
+    hands = np.ascontiguousarray(hands, dtype=fmt[0]) if fmt else np.ascontiguousarray(hands)   # (an unknown format is the library's to refuse)
+    n = hands.size // (fmt[1] if fmt else 1)
     out = np.empty(n, dtype=np.uint16 if key_format == E.KEY_CLASS16 else np.uint32)
     E.check(E.lib().mc_eval_batch(hands.ctypes.data, in_format, n, out.ctypes.data, key_format, stage_cards))
     return out

@@ -590,6 +590,142 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
     if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// K2, warp-cooperative walk (default).  In colex order the hands that share their four highest cards c3 < c4 < c5 < c6
+// are one contiguous run of C(c3, 3) indices, and inside the run the index IS the colex rank of the three low cards
+// (c0, c1, c2 < c3): C(c2, 3) + pair index.  A warp takes a contiguous index range and walks the runs inside it; its lanes
+// stride the three-card index, so every lane does the same thing every step -- no colex carry diverges a warp (the
+// per-thread walk pays the carry path of ANY lane in 98 % of its steps: 61.5 executed instructions per hand against 41
+// on the common step).  Per hand: one 8-byte load of the pair's {rank-key sum, suit counters} from a table of all 1,326
+// pairs (consecutive lanes read consecutive entries), two adds onto the run's partial hand + card c2 (kept per lane,
+// advanced when the three-card index crosses C(c2 + 1, 3)), the two hash loads; the pair's mask words are only loaded by
+// the lanes whose hand holds a flush.  Lane utilisation over the whole enumeration: 97.2 % (runs end mid-warp).
+// ---------------------------------------------------------------------------------------------------
+constexpr int N_PAIRS = 1326;
+__global__ void __launch_bounds__(ENUM_THREADS, 1)
+enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
+                  const uint32_t *__restrict__ g_nib, int n_classes, const __grid_constant__ CatBase cb,
+                  unsigned long long *__restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));            // [52] by card id: {rk, sn, mlo, mhi}
+    uint4 *scat = sdeck + 52;                                                         // 16 entries: {dense base, counter increments lo / hi, 0}
+    uint2 *pairA = reinterpret_cast<uint2 *>(scat + 16);                              // [1326] {rk0 + rk1, sn0 + sn1} by colex pair index
+    uint2 *pairB = pairA + N_PAIRS;                                                   // [1326] {mlo, mhi}
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(pairB + N_PAIRS);   // 16 words
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
+    uint32_t *snib = sbin + BIN_N * BIN_K;
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
+    fill_binom(sbin);
+    for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
+    for (int p = threadIdx.x; p < N_PAIRS; p += blockDim.x) {
+        int c1 = 1;
+        while ((c1 + 1) * c1 / 2 <= p) c1++;                                          // largest c1 with C(c1, 2) <= p
+        const int c0 = p - c1 * (c1 - 1) / 2;
+        const int p0 = c0 + 2 + 3 * (c0 / 13), p1 = c1 + 2 + 3 * (c1 / 13);           // card id -> bit position
+        const uint4 a = live_entry(g_card[p0], p0), b = live_entry(g_card[p1], p1);
+        pairA[p] = make_uint2(a.x + b.x, a.y + b.y);
+        pairB[p] = make_uint2(a.z | b.z, a.w | b.w);
+    }
+    if (threadIdx.x < 52) { const int id = threadIdx.x, p = id + 2 + 3 * (id / 13); sdeck[id] = live_entry(g_card[p], p); }
+    if (threadIdx.x < 16) {
+        const int c = threadIdx.x;                                   // categories 0..3: 8-bit fields of lo; 4..8: 6-bit fields of hi
+        sred[c] = 0ull;
+        scat[c] = make_uint4(c < 10 ? cb.v[c] : 0u, c < 4 ? 1u << (8 * c) : 0u, (c >= 4 && c < 9) ? 1u << (6 * (c - 4)) : 0u, 0u);
+    }
+    stage.wait();
+    const uint32_t tbl = staged_table_base(H);
+
+    uint32_t h[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) h[i] = 0;
+    unsigned long long sumN = 0;
+    uint32_t acc_lo = 0, acc_hi = 0, nsum = 0, nfold = 0;            // nsum <= 32 * 2^24
+    auto fold = [&]() {
+#pragma unroll
+        for (int i = 0; i < 4; i++) h[i] += (acc_lo >> (8 * i)) & 255u;
+#pragma unroll
+        for (int i = 4; i < 9; i++) h[i] += (acc_hi >> (6 * (i - 4))) & 63u;
+        sumN += nsum;
+        acc_lo = acc_hi = nsum = nfold = 0;
+    };
+    const int lane = threadIdx.x & 31;
+    const uint64_t nw = (uint64_t)gridDim.x * (ENUM_THREADS / 32), gw = (uint64_t)blockIdx.x * (ENUM_THREADS / 32) + (threadIdx.x >> 5);
+    const uint64_t per = (count + nw - 1) / nw;
+    const uint64_t lo = gw * per < count ? gw * per : count;
+    const uint64_t hi = lo + per < count ? lo + per : count;
+    if (lo < hi) {
+        // the run the range starts in: its four high cards and the three-card index inside it (warp-uniform)
+        uint32_t idx = (uint32_t)(first + lo);
+        int c[7], x = 52;
+#pragma unroll
+        for (int k = 7; k >= 4; k--) {
+            x--;
+            while (sbin[x * BIN_K + k] > idx) x--;
+            c[k - 1] = x;
+            idx -= sbin[x * BIN_K + k];
+        }
+        uint32_t i0 = idx, remaining = (uint32_t)(hi - lo);
+        for (;;) {
+            const uint32_t size3 = sbin[c[3] * BIN_K + 3];
+            const uint32_t iend = min(size3, i0 + remaining);
+            const uint4 d3 = sdeck[c[3]], d4 = sdeck[c[4]], d5 = sdeck[c[5]], d6 = sdeck[c[6]];
+            const HandState P{d3.x + d4.x + d5.x + d6.x, SN_BIAS + d3.y + d4.y + d5.y + d6.y, d3.z | d4.z | d5.z | d6.z, d3.w | d4.w | d5.w | d6.w};
+            uint32_t i = i0 + (uint32_t)lane;
+            if (i < iend) {
+                uint32_t c2 = 2;                                     // largest c2 with C(c2, 3) <= i; c2 < c3 <= 48
+#pragma unroll
+                for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = c2 + step; if (y <= 51u && sbin[y * BIN_K + 3] <= i) c2 = y; }
+                uint32_t t3c = sbin[c2 * BIN_K + 3], t3n = sbin[(c2 + 1) * BIN_K + 3];
+                uint4 e2 = sdeck[c2];
+                HandState Q{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
+                for (; i < iend; i += 32) {
+                    while (i >= t3n) {                               // the three-card index entered the next c2
+                        c2++; t3c = t3n; t3n = sbin[(c2 + 1) * BIN_K + 3];
+                        e2 = sdeck[c2];
+                        Q = HandState{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
+                    }
+                    const uint32_t p = i - t3c;
+                    const uint2 A = pairA[p];
+                    const uint32_t t = Q.t + A.x, sn = Q.sn + A.y, flag = sn & 0x8888u;
+                    uint32_t addr = hb_slot_addr(t, tbl);
+                    if (flag) {                                      // one of 0x8, 0x80, 0x800, 0x8000: the flush suit's lane
+                        const uint2 B = pairB[p];
+                        const uint32_t w = (flag & 0x8800u) ? (Q.mhi | B.y) : (Q.mlo | B.x);
+                        addr = hb_flush_addr(((flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu)) >> 2, tbl);
+                    }
+                    const uint32_t code = lds_u16(addr);
+                    const uint4 ci = scat[code >> 12];
+                    acc_lo += ci.y; acc_hi += ci.z;
+                    nsum += snib[ci.x + (code & 0xFFFu)];
+                    if (++nfold == ENUM_FOLD) fold();
+                }
+            }
+            remaining -= iend - i0;
+            if (remaining == 0) break;
+            i0 = 0;                                                  // next run: colex successor of (c3, c4, c5, c6)
+            c[3]++;
+            if (c[3] == c[4]) { c[3] = 3; c[4]++; if (c[4] == c[5]) { c[4] = 4; c[5]++; if (c[5] == c[6]) { c[5] = 5; c[6]++; } } }
+        }
+    }
+    fold();
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const uint32_t s = warp_sum(h[i]);
+        if (lane == 0 && s) atomicAdd(&sred[i], (unsigned long long)s);
+    }
+    sumN = warp_sum64(sumN);
+    if (lane == 0) atomicAdd(&sred[9], sumN);
+    __syncthreads();
+    if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
+}
+static size_t enum_warp_smem(int n_classes) {
+    return sizeof(HashBlob) + (52 + 16) * sizeof(uint4) + 2 * N_PAIRS * sizeof(uint2) + 16 * sizeof(unsigned long long) +
+           (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
+}
+
 static size_t enum_smem(int n_classes) {
     return sizeof(HashBlob) + (LIVE_MAX * 32 + 16) * sizeof(uint4) + 16 * sizeof(unsigned long long) +
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
@@ -598,6 +734,18 @@ static size_t enum_smem(int n_classes) {
 cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out,
                               const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (count == 0) return cudaSuccess;
+    // MCP_K2_VARIANT=thread selects the per-thread colex walk (A/B arm of tools/k2_time.py); default: warp-cooperative
+    static const bool per_thread = [] { const char *e = getenv("MCP_K2_VARIANT"); return e && e[0] == 't'; }();
+    if (!per_thread) {
+        const size_t wsmem = enum_warp_smem((int)tb.n_classes);
+        cudaError_t e = cudaFuncSetAttribute(enum7_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
+        if (e != cudaSuccess) return e;
+        uint64_t want = (count + 32 * 64 - 1) / (32 * 64);           // at least 64 hands per lane before another warp is worth it
+        want = (want + ENUM_THREADS / 32 - 1) / (ENUM_THREADS / 32);
+        const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : (want < 1 ? 1 : want));
+        enum7_warp_kernel<<<grid, ENUM_THREADS, wsmem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, tb.cat_base, d_out);
+        return cudaGetLastError();
+    }
     const size_t smem = enum_smem((int)tb.n_classes);
     cudaError_t e = cudaFuncSetAttribute(enum7_hash_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -1,5 +1,5 @@
-"""Times K3 on BASELINE config 3 (A-A vs K-K, all C(48,5) boards) with CUDA events, golden counts checked.
-MCP_CLUSTER=1 launches without thread-block clusters (A/B of the multicast table staging)."""
+"""Times K3 on BASELINE config 3 (A-A vs K-K, all C(48,5) boards) with CUDA events, golden counts checked, and the
+fixed cost of a launch (one board; one board per thread)."""
 import ctypes as C
 import os
 import sys
@@ -29,4 +29,18 @@ b.record()
 torch.cuda.synchronize()
 c = cnt.tolist()
 ok = (c[0], c[1], c[9]) == (1388072 * reps, 318176 * reps, 6056 * reps)
-print("K3 cluster=%s: %.2f us per launch (back to back), golden counts %s" % (os.environ.get("MCP_CLUSTER", "2"), 1e3 * a.elapsed_time(b) / reps, ok))
+print("K3: %.2f us per launch (back to back), golden counts %s" % (1e3 * a.elapsed_time(b) / reps, ok))
+# the fixed cost of a launch: the same kernel over ONE board (launch + table staging + counter flush)
+a.record()
+for _ in range(reps):
+    E.check(L.mc_equity_exhaustive_dev(holes, 2, 0, 0, 0, 1, cnt.data_ptr(), st))
+b.record()
+torch.cuda.synchronize()
+print("K3 over one board (launch + staging floor, 1 block): %.2f us" % (1e3 * a.elapsed_time(b) / reps))
+for nb in (151552, 151552 * 4):
+    a.record()
+    for _ in range(reps):
+        E.check(L.mc_equity_exhaustive_dev(holes, 2, 0, 0, 0, nb, cnt.data_ptr(), st))
+    b.record()
+    torch.cuda.synchronize()
+    print("K3 over %d boards (148 blocks): %.2f us" % (nb, 1e3 * a.elapsed_time(b) / reps))
