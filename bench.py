@@ -325,7 +325,9 @@ def run_ours(args):
                            "parity_checked": True if rank == 0 else None,
                            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
                                         "kernel": "eval_stream_hash_kernel<6, Lay56, uint32_t>"}}
-    E.check(L.mc_random_hands_dev(SEED, rank * n, n, 7, masks.data_ptr(), stream))       # back to the river hands for e2e
+    E.check(L.mc_random_hands_dev(SEED, rank * n, n, 7, masks.data_ptr(), stream))       # back to the river hands (and their keys) for e2e
+    k1_step()
+    torch.cuda.synchronize()
 
     # ---- e2e: the host-buffer C-ABI calls, pinned memory, H2D + kernels + D2H inside the timed region ----
     # Three wire formats of the same batch call, all bound by the host link:

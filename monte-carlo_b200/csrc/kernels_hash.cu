@@ -674,34 +674,37 @@ enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
             const uint4 d3 = sdeck[c[3]], d4 = sdeck[c[4]], d5 = sdeck[c[5]], d6 = sdeck[c[6]];
             const HandState P{d3.x + d4.x + d5.x + d6.x, SN_BIAS + d3.y + d4.y + d5.y + d6.y, d3.z | d4.z | d5.z | d6.z, d3.w | d4.w | d5.w | d6.w};
             uint32_t i = i0 + (uint32_t)lane;
-            if (i < iend) {
-                uint32_t c2 = 2;                                     // largest c2 with C(c2, 3) <= i; c2 < c3 <= 48
+            const uint32_t rounds = (iend - i0 + 31u) >> 5;           // warp-uniform: every lane runs the same trip count
+            uint32_t c2 = 2;                                         // largest c2 with C(c2, 3) <= i; c2 < c3 <= 48
+            {
+                const uint32_t ic = min(i, iend - 1u);               // (a lane past the end of a short run idles on a valid index)
 #pragma unroll
-                for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = c2 + step; if (y <= 51u && sbin[y * BIN_K + 3] <= i) c2 = y; }
-                uint32_t t3c = sbin[c2 * BIN_K + 3], t3n = sbin[(c2 + 1) * BIN_K + 3];
-                uint4 e2 = sdeck[c2];
-                HandState Q{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
-                for (; i < iend; i += 32) {
-                    while (i >= t3n) {                               // the three-card index entered the next c2
-                        c2++; t3c = t3n; t3n = sbin[(c2 + 1) * BIN_K + 3];
-                        e2 = sdeck[c2];
-                        Q = HandState{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
-                    }
-                    const uint32_t p = i - t3c;
-                    const uint2 A = pairA[p];
-                    const uint32_t t = Q.t + A.x, sn = Q.sn + A.y, flag = sn & 0x8888u;
-                    uint32_t addr = hb_slot_addr(t, tbl);
-                    if (flag) {                                      // one of 0x8, 0x80, 0x800, 0x8000: the flush suit's lane
-                        const uint2 B = pairB[p];
-                        const uint32_t w = (flag & 0x8800u) ? (Q.mhi | B.y) : (Q.mlo | B.x);
-                        addr = hb_flush_addr(((flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu)) >> 2, tbl);
-                    }
-                    const uint32_t code = lds_u16(addr);
-                    const uint4 ci = scat[code >> 12];
-                    acc_lo += ci.y; acc_hi += ci.z;
-                    nsum += snib[ci.x + (code & 0xFFFu)];
-                    if (++nfold == ENUM_FOLD) fold();
+                for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = min(c2 + step, 51u); if (sbin[y * BIN_K + 3] <= ic) c2 = y; }
+            }
+            uint32_t t3c = sbin[c2 * BIN_K + 3], t3n = sbin[(c2 + 1) * BIN_K + 3];
+            uint4 e2 = sdeck[c2];
+            HandState Q{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
+            for (uint32_t r = 0; r < rounds; r++, i += 32) {
+                const bool live = i < iend;
+                while (live && i >= t3n) {                           // the three-card index entered the next c2
+                    c2++; t3c = t3n; t3n = sbin[(c2 + 1) * BIN_K + 3];
+                    e2 = sdeck[c2];
+                    Q = HandState{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
                 }
+                const uint32_t p = live ? i - t3c : 0u;
+                const uint2 A = pairA[p];
+                const uint32_t t = Q.t + A.x, sn = Q.sn + A.y, flag = sn & 0x8888u;
+                uint32_t addr = hb_slot_addr(t, tbl);
+                if (flag) {                                          // one of 0x8, 0x80, 0x800, 0x8000: the flush suit's lane
+                    const uint2 B = pairB[p];
+                    const uint32_t w = (flag & 0x8800u) ? (Q.mhi | B.y) : (Q.mlo | B.x);
+                    addr = hb_flush_addr(((flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu)) >> 2, tbl);
+                }
+                const uint32_t code = lds_u16(addr);
+                const uint4 ci = scat[live ? code >> 12 : 15u];      // entry 15 is all zero: an idle lane counts nothing
+                acc_lo += ci.y; acc_hi += ci.z;
+                nsum += live ? snib[ci.x + (code & 0xFFFu)] : 0u;
+                if (++nfold == ENUM_FOLD) fold();                    // nfold counts rounds: uniform over the warp
             }
             remaining -= iend - i0;
             if (remaining == 0) break;
