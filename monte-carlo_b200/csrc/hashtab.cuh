@@ -14,8 +14,9 @@
 // scramble of the multiset id whose bits 1..13 pick a bucket and bits 16..31 a slot; D holds the per-bucket
 // displacement found by first-fit (hash-and-displace, built at mc_init by hashtab_build.h).
 //
-// A table value ("class code") is cat << 12 | index of the value inside its category in ascending order, so
-// unsigned order of codes == clojure.core/compare order of [cat hit kick], and cat = code >> 12.
+// A table value ("class code") is the dense index of the value in the ascending list of the 4,892 values seven cards
+// can make, so unsigned order of codes == clojure.core/compare order of [cat hit kick]; nib_keys[code] is the public
+// key and cat_base[] (first code of each category) gives the category.
 #pragma once
 #include <cstdint>
 #include "eval.cuh"

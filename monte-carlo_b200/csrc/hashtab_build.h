@@ -2,7 +2,7 @@
 // it never evaluates a hand.  The caller supplies, for every 7-card rank multiset and every 5..7-card flush lane,
 // the packed key of a representative hand (mc_init computes them ON THE GPU with the bit-plane evaluator of
 // eval.cuh; tests/host_check.cpp computes them with the same header compiled for the host), and gets back
-//   blob      D / F / V of hashtab.cuh, values = class codes (cat << 12 | index inside the category)
+//   blob      D / F / V of hashtab.cuh, values = class codes (dense index of the value in ascending order)
 //   nib_keys  dense class index -> public nibble key (ascending)
 //   cat_base  dense index of the first class of each category (cat_base[9] = number of classes)
 #pragma once
@@ -70,13 +70,13 @@ inline std::string ht_build(const std::vector<HashRep> &reps, const std::vector<
     std::vector<uint16_t> code(keys.size());
     T->nib_keys.resize(keys.size());
     for (int c = 0; c <= 9; c++) T->cat_base[c] = (uint32_t)keys.size();
-    uint32_t prev_cat = 99, idx = 0;
+    if (keys.size() >= 65535) return "more than 65534 classes";
+    uint32_t prev_cat = 99;
     for (size_t i = 0; i < keys.size(); i++) {
         const uint32_t cat = keys[i] >> 28;
         if (cat > 8) return "a representative evaluated to an invalid key";
-        if (cat != prev_cat) { idx = 0; prev_cat = cat; T->cat_base[cat] = (uint32_t)i; }
-        if (idx >= 4096) return "more than 4096 classes in one category";
-        code[i] = (uint16_t)(cat << 12 | idx++);
+        if (cat != prev_cat) { prev_cat = cat; T->cat_base[cat] = (uint32_t)i; }
+        code[i] = (uint16_t)i;                       // class code = dense index of the value in ascending order
         T->nib_keys[i] = packed_to_nibble(keys[i]);
     }
     for (int c = 8; c >= 0; c--) if (T->cat_base[c] == keys.size() && c < 9) T->cat_base[c] = T->cat_base[c + 1];

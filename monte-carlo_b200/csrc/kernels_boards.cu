@@ -93,7 +93,7 @@ pf_board_eval_kernel(const PfBoard *__restrict__ boards, int nb, const HashBlob 
                 const uint32_t d = lds_u16(tbl + (t & 0x3FFEu));
                 const uint32_t va = tbl + HT_BUCKETS * 2 + HT_FLUSH * 2 + 2u * ((t >> 16) + d), fa = tbl + HT_BUCKETS * 2 + 2u * (ln >> 2);
                 const uint32_t code = lds_u16(flag ? fa : va);
-                dense[r] = cb.v[code >> 12] + (code & 0xFFFu);
+                dense[r] = code;                                   // class codes are dense indices
                 info[r] = dense[r] << 8 | pb_class_of(p1, p2);
                 atomicAdd(&shist[dense[r]], 1u);
             }

@@ -566,9 +566,10 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
             for (uint32_t j = 0; j < len; j++) {
                 const HandState s = w.hand();
                 const uint32_t code = hb_class(s.t, s.sn, s.mlo, s.mhi, tbl);
-                const uint4 ci = scat[code >> 12];
+                const uint32_t nib = snib[code];                      // class codes are dense indices; cat = key >> 20
+                const uint4 ci = scat[nib >> 20];
                 acc_lo += ci.y; acc_hi += ci.z;
-                nsum += snib[ci.x + (code & 0xFFFu)];
+                nsum += nib;
                 w.next(my_deck, 52);
             }
 #pragma unroll
@@ -593,33 +594,35 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
 // ---------------------------------------------------------------------------------------------------
 // K2, warp-cooperative walk (default).  In colex order the hands that share their four highest cards c3 < c4 < c5 < c6
 // are one contiguous run of C(c3, 3) indices, and inside the run the index IS the colex rank of the three low cards
-// (c0, c1, c2 < c3): C(c2, 3) + pair index.  A warp takes a contiguous index range and walks the runs inside it; its lanes
+// (c0, c1, c2 < c3): C(c2, 3) + pair index.  A warp takes chunks of 1,024 consecutive indices and walks the runs inside; its lanes
 // stride the three-card index, so every lane does the same thing every step -- no colex carry diverges a warp (the
 // per-thread walk pays the carry path of ANY lane in 98 % of its steps: 61.5 executed instructions per hand against 41
 // on the common step).  Per hand: one 8-byte load of the pair's {rank-key sum, suit counters} from a table of all 1,326
 // pairs (consecutive lanes read consecutive entries), two adds onto the run's partial hand + card c2 (kept per lane,
 // advanced when the three-card index crosses C(c2 + 1, 3)), the two hash loads; the pair's mask words are only loaded by
-// the lanes whose hand holds a flush.  Lane utilisation over the whole enumeration: 97.2 % (runs end mid-warp).
+// the lanes whose hand holds a flush.  Counting is one shared-memory reduction per hand into a histogram of the 4,892 class
+// codes; categories and the key checksum come out of it once per block.  Lane utilisation over the whole enumeration:
+// 97.2 % (runs end mid-warp).
 // ---------------------------------------------------------------------------------------------------
 constexpr int N_PAIRS = 1326;
+constexpr uint32_t EW_CHUNK = 1024;           // hands per unit of work: chunks are dealt round-robin to the warps, so the slow
+                                              // stretches of the enumeration (low indices: runs of a few hands) spread over all of them
 __global__ void __launch_bounds__(ENUM_THREADS, 1)
 enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
-                  const uint32_t *__restrict__ g_nib, int n_classes, const __grid_constant__ CatBase cb,
-                  unsigned long long *__restrict__ out) {
+                  const uint32_t *__restrict__ g_nib, int n_classes, unsigned long long *__restrict__ out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
     uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));            // [52] by card id: {rk, sn, mlo, mhi}
-    uint4 *scat = sdeck + 52;                                                         // 16 entries: {dense base, counter increments lo / hi, 0}
-    uint2 *pairA = reinterpret_cast<uint2 *>(scat + 16);                              // [1326] {rk0 + rk1, sn0 + sn1} by colex pair index
+    uint2 *pairA = reinterpret_cast<uint2 *>(sdeck + 52);                             // [1326] {rk0 + rk1, sn0 + sn1} by colex pair index
     uint2 *pairB = pairA + N_PAIRS;                                                   // [1326] {mlo, mhi}
     unsigned long long *sred = reinterpret_cast<unsigned long long *>(pairB + N_PAIRS);   // 16 words
     uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
-    uint32_t *snib = sbin + BIN_N * BIN_K;
+    uint32_t *shist = sbin + BIN_N * BIN_K;                                           // [n_classes] hands per class code
     __shared__ unsigned long long mbar;
     BulkStage stage;
     stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
     fill_binom(sbin);
-    for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
+    for (int i = threadIdx.x; i < n_classes; i += blockDim.x) shist[i] = 0u;
     for (int p = threadIdx.x; p < N_PAIRS; p += blockDim.x) {
         int c1 = 1;
         while ((c1 + 1) * c1 / 2 <= p) c1++;                                          // largest c1 with C(c1, 2) <= p
@@ -630,41 +633,25 @@ enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
         pairB[p] = make_uint2(a.z | b.z, a.w | b.w);
     }
     if (threadIdx.x < 52) { const int id = threadIdx.x, p = id + 2 + 3 * (id / 13); sdeck[id] = live_entry(g_card[p], p); }
-    if (threadIdx.x < 16) {
-        const int c = threadIdx.x;                                   // categories 0..3: 8-bit fields of lo; 4..8: 6-bit fields of hi
-        sred[c] = 0ull;
-        scat[c] = make_uint4(c < 10 ? cb.v[c] : 0u, c < 4 ? 1u << (8 * c) : 0u, (c >= 4 && c < 9) ? 1u << (6 * (c - 4)) : 0u, 0u);
-    }
+    if (threadIdx.x < 16) sred[threadIdx.x] = 0ull;
     stage.wait();
     const uint32_t tbl = staged_table_base(H);
+    const uint32_t hist32 = staged_table_base(shist);
 
-    uint32_t h[9];
-#pragma unroll
-    for (int i = 0; i < 9; i++) h[i] = 0;
-    unsigned long long sumN = 0;
-    uint32_t acc_lo = 0, acc_hi = 0, nsum = 0, nfold = 0;            // nsum <= 32 * 2^24
-    auto fold = [&]() {
-#pragma unroll
-        for (int i = 0; i < 4; i++) h[i] += (acc_lo >> (8 * i)) & 255u;
-#pragma unroll
-        for (int i = 4; i < 9; i++) h[i] += (acc_hi >> (6 * (i - 4))) & 63u;
-        sumN += nsum;
-        acc_lo = acc_hi = nsum = nfold = 0;
-    };
     const int lane = threadIdx.x & 31;
     const uint64_t nw = (uint64_t)gridDim.x * (ENUM_THREADS / 32), gw = (uint64_t)blockIdx.x * (ENUM_THREADS / 32) + (threadIdx.x >> 5);
-    const uint64_t per = (count + nw - 1) / nw;
-    const uint64_t lo = gw * per < count ? gw * per : count;
-    const uint64_t hi = lo + per < count ? lo + per : count;
-    if (lo < hi) {
-        // the run the range starts in: its four high cards and the three-card index inside it (warp-uniform)
+    for (uint64_t lo = gw * EW_CHUNK; lo < count; lo += nw * EW_CHUNK) {
+        const uint64_t hi = lo + EW_CHUNK < count ? lo + EW_CHUNK : count;
+        // the run the chunk starts in: its four high cards and the three-card index inside it (warp-uniform; four
+        // branch-free binary searches: the largest x with C(x, k) <= rest is below the previous card by itself)
         uint32_t idx = (uint32_t)(first + lo);
-        int c[7], x = 52;
+        int c[7];
 #pragma unroll
         for (int k = 7; k >= 4; k--) {
-            x--;
-            while (sbin[x * BIN_K + k] > idx) x--;
-            c[k - 1] = x;
+            uint32_t x = (uint32_t)k - 1u;
+#pragma unroll
+            for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = min(x + step, 52u); if (sbin[y * BIN_K + k] <= idx) x = y; }
+            c[k - 1] = (int)x;
             idx -= sbin[x * BIN_K + k];
         }
         uint32_t i0 = idx, remaining = (uint32_t)(hi - lo);
@@ -701,10 +688,9 @@ enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
                     addr = hb_flush_addr(((flag & 0x8080u) ? (w >> 16) : (w & 0xFFFFu)) >> 2, tbl);
                 }
                 const uint32_t code = lds_u16(addr);
-                const uint4 ci = scat[live ? code >> 12 : 15u];      // entry 15 is all zero: an idle lane counts nothing
-                acc_lo += ci.y; acc_hi += ci.z;
-                nsum += live ? snib[ci.x + (code & 0xFFFu)] : 0u;
-                if (++nfold == ENUM_FOLD) fold();                    // nfold counts rounds: uniform over the warp
+                // one shared-memory reduction per hand into the histogram of the 4,892 class codes; categories and the
+                // key checksum are derived from it once per block
+                if (live) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(hist32 + 4u * code) : "memory");
             }
             remaining -= iend - i0;
             if (remaining == 0) break;
@@ -713,19 +699,21 @@ enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
             if (c[3] == c[4]) { c[3] = 3; c[4]++; if (c[4] == c[5]) { c[4] = 4; c[5]++; if (c[5] == c[6]) { c[5] = 5; c[6]++; } } }
         }
     }
-    fold();
-#pragma unroll
-    for (int i = 0; i < 9; i++) {
-        const uint32_t s = warp_sum(h[i]);
-        if (lane == 0 && s) atomicAdd(&sred[i], (unsigned long long)s);
+    __syncthreads();
+    // class histogram -> categories (key >> 20) and key checksum
+    for (int cl = threadIdx.x; cl < n_classes; cl += blockDim.x) {
+        const uint32_t n = shist[cl];
+        if (n) {
+            const uint32_t nib = g_nib[cl];
+            atomicAdd(&sred[nib >> 20], (unsigned long long)n);
+            atomicAdd(&sred[9], (unsigned long long)n * nib);
+        }
     }
-    sumN = warp_sum64(sumN);
-    if (lane == 0) atomicAdd(&sred[9], sumN);
     __syncthreads();
     if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
 }
 static size_t enum_warp_smem(int n_classes) {
-    return sizeof(HashBlob) + (52 + 16) * sizeof(uint4) + 2 * N_PAIRS * sizeof(uint2) + 16 * sizeof(unsigned long long) +
+    return sizeof(HashBlob) + 52 * sizeof(uint4) + 2 * N_PAIRS * sizeof(uint2) + 16 * sizeof(unsigned long long) +
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
 }
 
@@ -743,10 +731,10 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
         const size_t wsmem = enum_warp_smem((int)tb.n_classes);
         cudaError_t e = cudaFuncSetAttribute(enum7_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
         if (e != cudaSuccess) return e;
-        uint64_t want = (count + 32 * 64 - 1) / (32 * 64);           // at least 64 hands per lane before another warp is worth it
+        uint64_t want = (count + EW_CHUNK - 1) / EW_CHUNK;            // one chunk per warp before another block is worth it
         want = (want + ENUM_THREADS / 32 - 1) / (ENUM_THREADS / 32);
         const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : (want < 1 ? 1 : want));
-        enum7_warp_kernel<<<grid, ENUM_THREADS, wsmem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, tb.cat_base, d_out);
+        enum7_warp_kernel<<<grid, ENUM_THREADS, wsmem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, d_out);
         return cudaGetLastError();
     }
     const size_t smem = enum_smem((int)tb.n_classes);

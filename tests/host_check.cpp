@@ -94,7 +94,7 @@ static int check_hash() {
             uint64_t m = 0; uint32_t t = 0, sn = mcp::SN_BIAS;
             for (int j = 0; j < 7; j++) { const int p = 16 * (c[j] / 13) + c[j] % 13 + 2; m |= 1ull << p; t += T.card[p].rk; sn += T.card[p].sn; }
             const uint32_t code = mcp::ht_class(t, sn, (uint32_t)m, (uint32_t)(m >> 32), T.blob.D, T.blob.F, T.blob.V);
-            const uint32_t got = T.nib_keys[T.cat_base[code >> 12] + (code & 0xFFFu)];
+            const uint32_t got = T.nib_keys[code];
             const uint32_t want = orc_eval_mask(m);
             if (stream_key(m) != want) { if (kbad < 5) fprintf(stderr, "STREAM BLOB MISMATCH mask=%016llx\n", (unsigned long long)m); kbad++; }
             const uint32_t gid = stream_lookup<mcp::Lay7>(IM.cls7, SH, m);
