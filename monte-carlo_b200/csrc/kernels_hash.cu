@@ -592,7 +592,7 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K2, warp-cooperative walk (default).  In colex order the hands that share their four highest cards c3 < c4 < c5 < c6
+// K2, warp-cooperative walk (A/B variant, MCP_K2_VARIANT=warp; measured slower than the per-thread walk, see the launcher).  In colex order the hands that share their four highest cards c3 < c4 < c5 < c6
 // are one contiguous run of C(c3, 3) indices, and inside the run the index IS the colex rank of the three low cards
 // (c0, c1, c2 < c3): C(c2, 3) + pair index.  A warp takes chunks of 1,024 consecutive indices and walks the runs inside; its lanes
 // stride the three-card index, so every lane does the same thing every step -- no colex carry diverges a warp (the
@@ -605,8 +605,9 @@ enum7_hash_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
 // 97.2 % (runs end mid-warp).
 // ---------------------------------------------------------------------------------------------------
 constexpr int N_PAIRS = 1326;
-constexpr uint32_t EW_CHUNK = 1024;           // hands per unit of work: chunks are dealt round-robin to the warps, so the slow
+constexpr uint32_t EW_CHUNK = 4096;           // hands per unit of work: chunks are dealt round-robin to the warps, so the slow
                                               // stretches of the enumeration (low indices: runs of a few hands) spread over all of them
+constexpr uint32_t EW_HEAD = 1u << 21;        // ... and the slowest stretch, the first 2 Mi indices, goes out in chunks of 256
 __global__ void __launch_bounds__(ENUM_THREADS, 1)
 enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
                   const uint32_t *__restrict__ g_nib, int n_classes, unsigned long long *__restrict__ out) {
@@ -640,8 +641,17 @@ enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
 
     const int lane = threadIdx.x & 31;
     const uint64_t nw = (uint64_t)gridDim.x * (ENUM_THREADS / 32), gw = (uint64_t)blockIdx.x * (ENUM_THREADS / 32) + (threadIdx.x >> 5);
-    for (uint64_t lo = gw * EW_CHUNK; lo < count; lo += nw * EW_CHUNK) {
-        const uint64_t hi = lo + EW_CHUNK < count ? lo + EW_CHUNK : count;
+    // work list: [0, head) in chunks of 256, the rest in chunks of EW_CHUNK, both dealt round-robin
+    const uint64_t head = first < EW_HEAD ? (EW_HEAD - first < count ? EW_HEAD - first : count) : 0;
+    const uint64_t n_head = (head + 255) >> 8, n_all = n_head + (count - head + EW_CHUNK - 1) / EW_CHUNK;
+    // (lane-constant) where index `lane` of a run sits: the run's three-card index starts at 0 in all but a chunk's first run
+    uint32_t c2_lane = 2;
+    while (sbin[(c2_lane + 1) * BIN_K + 3] <= (uint32_t)lane) c2_lane++;
+    for (uint64_t ch = gw; ch < n_all; ch += nw) {
+        const uint64_t lo = ch < n_head ? ch << 8 : head + (ch - n_head) * EW_CHUNK;
+        const uint64_t top = ch < n_head ? head : count;
+        const uint64_t len = ch < n_head ? 256 : EW_CHUNK;
+        const uint64_t hi = lo + len < top ? lo + len : top;
         // the run the chunk starts in: its four high cards and the three-card index inside it (warp-uniform; four
         // branch-free binary searches: the largest x with C(x, k) <= rest is below the previous card by itself)
         uint32_t idx = (uint32_t)(first + lo);
@@ -662,12 +672,13 @@ enum7_warp_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g
             const HandState P{d3.x + d4.x + d5.x + d6.x, SN_BIAS + d3.y + d4.y + d5.y + d6.y, d3.z | d4.z | d5.z | d6.z, d3.w | d4.w | d5.w | d6.w};
             uint32_t i = i0 + (uint32_t)lane;
             const uint32_t rounds = (iend - i0 + 31u) >> 5;           // warp-uniform: every lane runs the same trip count
-            uint32_t c2 = 2;                                         // largest c2 with C(c2, 3) <= i; c2 < c3 <= 48
-            {
-                const uint32_t ic = min(i, iend - 1u);               // (a lane past the end of a short run idles on a valid index)
+            uint32_t c2 = c2_lane;                                   // largest c2 with C(c2, 3) <= i; c2 < c3 <= 48
+            if (i0 != 0) {                                           // (uniform) a chunk's first run starts anywhere
+                c2 = 2;
 #pragma unroll
-                for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = min(c2 + step, 51u); if (sbin[y * BIN_K + 3] <= ic) c2 = y; }
+                for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = min(c2 + step, 51u); if (sbin[y * BIN_K + 3] <= i) c2 = y; }
             }
+            c2 = min(c2, (uint32_t)c[3] - 1u);                       // (a lane past the end of a short run idles on a valid card)
             uint32_t t3c = sbin[c2 * BIN_K + 3], t3n = sbin[(c2 + 1) * BIN_K + 3];
             uint4 e2 = sdeck[c2];
             HandState Q{P.t + e2.x, P.sn + e2.y, P.mlo | e2.z, P.mhi | e2.w};
@@ -725,8 +736,11 @@ static size_t enum_smem(int n_classes) {
 cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out,
                               const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (count == 0) return cudaSuccess;
-    // MCP_K2_VARIANT=thread selects the per-thread colex walk (A/B arm of tools/k2_time.py); default: warp-cooperative
-    static const bool per_thread = [] { const char *e = getenv("MCP_K2_VARIANT"); return e && e[0] == 't'; }();
+    // Two walks with identical results.  Default: the per-thread colex walk (0.406 ms for all C(52,7) hands on a B200).
+    // MCP_K2_VARIANT=warp selects the warp-cooperative walk (0.479 ms: its inner loop is 31 instructions per 32 hands
+    // against 41, but run starts, chunk starts and the lanes crossing C(c2, 3) boundaries bring it to 62 executed
+    // instructions per hand at IPC 2.2 -- profiles/r02_k2_warp_ncu.txt); kept as the A/B arm of tools/k2_time.py.
+    static const bool per_thread = [] { const char *e = getenv("MCP_K2_VARIANT"); return !(e && e[0] == 'w'); }();
     if (!per_thread) {
         const size_t wsmem = enum_warp_smem((int)tb.n_classes);
         cudaError_t e = cudaFuncSetAttribute(enum7_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
