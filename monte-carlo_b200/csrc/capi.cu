@@ -8,6 +8,9 @@
 #include "philox.cuh"
 #include "hashtab_build.h"
 
+#include <nccl.h>          // types only: the library is bound at run time (dlopen), see NcclApi
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <atomic>
 #include <cstdio>
@@ -84,6 +87,41 @@ struct DevCtx {
 // innermost function that takes it.)
 std::shared_mutex g_life;
 std::vector<std::unique_ptr<DevCtx>> g_ctx;
+
+// The one collective of the path: the int64 counts of the devices of this library instance are summed with a
+// single ncclAllReduce per device inside one group, over NVLink.  Single process, ncclCommInitAll.  NCCL is bound with
+// dlopen when mc_init is asked for it (MC_INIT_NCCL), so the library has no link-time dependency on it and a host that
+// drives one device per process (bench.py under torchrun) never loads it.  Without the flag the counts are summed on the
+// host from pinned copies: for 27 words that is the faster way (tools/collective_ab.py).
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    std::vector<ncclComm_t> comm;                   // one per context, same order as g_ctx
+    bool active() const { return !comm.empty(); }
+    std::string load() {
+        if (lib) return "";
+        lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) return std::string("libnccl.so.2 could not be loaded: ") + dlerror();
+        auto sym = [&](const char *n) { return dlsym(lib, n); };
+        CommInitAll = reinterpret_cast<decltype(CommInitAll)>(sym("ncclCommInitAll"));
+        CommDestroy = reinterpret_cast<decltype(CommDestroy)>(sym("ncclCommDestroy"));
+        AllReduce = reinterpret_cast<decltype(AllReduce)>(sym("ncclAllReduce"));
+        GroupStart = reinterpret_cast<decltype(GroupStart)>(sym("ncclGroupStart"));
+        GroupEnd = reinterpret_cast<decltype(GroupEnd)>(sym("ncclGroupEnd"));
+        GetErrorString = reinterpret_cast<decltype(GetErrorString)>(sym("ncclGetErrorString"));
+        if (!CommInitAll || !CommDestroy || !AllReduce || !GroupStart || !GroupEnd || !GetErrorString) return "libnccl.so.2 lacks a required symbol";
+        return "";
+    }
+    void destroy() {
+        for (ncclComm_t c : comm) if (c) CommDestroy(c);
+        comm.clear();
+    }
+} g_nccl;
 std::atomic<uint32_t> g_ticket_seq{1};              // tickets of the single-call kernels: process-wide, never 0, so a
                                                     // re-initialised context can never match a word left in pinned memory
 uint32_t next_ticket() { uint32_t t; do t = g_ticket_seq.fetch_add(1, std::memory_order_relaxed); while (t == 0); return t; }
@@ -181,7 +219,7 @@ int upload_tables(DevCtx &c) {
     return MC_OK;
 }
 
-int init_devices(const int *ids, int n) {
+int init_devices(const int *ids, int n, unsigned flags) {
     std::unique_lock<std::shared_mutex> lk(g_life);          // waits for every call in flight
     int visible = 0;
     cudaError_t e = cudaGetDeviceCount(&visible);
@@ -211,6 +249,17 @@ int init_devices(const int *ids, int n) {
         if (rc) return rc;
         fresh.push_back(std::move(c));
     }
+    // the collective, if asked for and if there is anything to reduce over
+    std::vector<ncclComm_t> comms;
+    if ((flags & MC_INIT_NCCL) && fresh.size() > 1) {
+        const std::string err = g_nccl.load();
+        if (!err.empty()) return fail(MC_ERR_CUDA, "MC_INIT_NCCL: " + err);
+        comms.assign(fresh.size(), nullptr);
+        const ncclResult_t r = g_nccl.CommInitAll(comms.data(), (int)want.size(), want.data());
+        if (r != ncclSuccess) return fail(MC_ERR_CUDA, std::string("ncclCommInitAll: ") + g_nccl.GetErrorString(r));
+    }
+    g_nccl.destroy();                                         // communicators of the contexts that go away
+    g_nccl.comm = comms;
     g_ctx.swap(fresh);                                        // the old contexts are destroyed with `fresh`
     return MC_OK;
 }
@@ -367,14 +416,25 @@ int sharded_small_job(uint64_t total, int words, unsigned long long *sum, F laun
         CU(cudaSetDevice(c.device));
         CU(cudaMemsetAsync(c.d_small, 0, SMALL_WORDS * sizeof(unsigned long long), c.stream));
         if (hi > lo) { rc = launch(c, lo, hi - lo); if (rc) return rc; }
-        CU(cudaMemcpyAsync(c.h_small, c.d_small, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+        if (!g_nccl.active()) CU(cudaMemcpyAsync(c.h_small, c.d_small, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c.stream));
+    }
+    if (g_nccl.active()) {
+        // one all-reduce per device inside one group, each on the stream its kernel ran on; device 0 delivers the sums
+        ncclResult_t r = g_nccl.GroupStart();
+        for (int d = 0; d < nd && r == ncclSuccess; d++)
+            r = g_nccl.AllReduce(g_ctx[d]->d_small, g_ctx[d]->d_small, (size_t)words, ncclUint64, ncclSum, g_nccl.comm[d], g_ctx[d]->stream);
+        const ncclResult_t e = g_nccl.GroupEnd();
+        if (r == ncclSuccess) r = e;
+        if (r != ncclSuccess) return fail(MC_ERR_CUDA, std::string("ncclAllReduce: ") + g_nccl.GetErrorString(r));
+        CU(cudaSetDevice(g_ctx[0]->device));
+        CU(cudaMemcpyAsync(g_ctx[0]->h_small, g_ctx[0]->d_small, words * sizeof(unsigned long long), cudaMemcpyDeviceToHost, g_ctx[0]->stream));
     }
     for (int i = 0; i < words; i++) sum[i] = 0;
     for (int d = 0; d < nd; d++) {
         DevCtx &c = *g_ctx[d];
         CU(cudaSetDevice(c.device));
         CU(cudaStreamSynchronize(c.stream));
-        for (int i = 0; i < words; i++) sum[i] += c.h_small[i];
+        if (d == 0 || !g_nccl.active()) for (int i = 0; i < words; i++) sum[i] += c.h_small[i];
     }
     return MC_OK;
 }
@@ -386,13 +446,18 @@ extern "C" {
 int mc_abi_version(void) { return 2; }
 const char *mc_last_error(void) { return g_err.c_str(); }
 
-int mc_init(int n_gpus, unsigned /*flags*/) { return init_devices(nullptr, n_gpus); }
+int mc_init(int n_gpus, unsigned flags) { return init_devices(nullptr, n_gpus, flags); }
 int mc_init_devices(const int *device_ids, int n) {
     if (!device_ids || n <= 0) return fail(MC_ERR_INVALID, "device_ids is empty");
-    return init_devices(device_ids, n);
+    return init_devices(device_ids, n, 0);
+}
+int mc_collective(void) {
+    std::shared_lock<std::shared_mutex> lk(g_life);
+    return g_nccl.active() ? 1 : 0;
 }
 void mc_shutdown(void) {
     std::unique_lock<std::shared_mutex> lk(g_life);          // waits for every call in flight
+    g_nccl.destroy();
     g_ctx.clear();
     g_tables.reset();
     g_images.reset();

@@ -19,7 +19,7 @@ MAX_SEATS = 9
 N_CLASSES = 169
 
 EXPORTS = [
-    "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version",
+    "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version", "mc_collective",
     "mc_card_bit", "mc_key_packed_to_nibble", "mc_key_decode",
     "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval_batch_packed48", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
     "mc_eval_batch", "mc_eval_batch_colex32", "mc_eval_batch_dev", "mc_unrank_colex32_dev", "mc_class_keys",
@@ -122,14 +122,17 @@ def check(rc):
 _initialised = False
 
 
-def init(n_gpus=0, devices=None):
+INIT_NCCL = 1
+
+
+def init(n_gpus=0, devices=None, flags=0):
     global _initialised
     L = lib()
     if devices is not None:
         arr = (C.c_int * len(devices))(*devices)
         check(L.mc_init_devices(arr, len(devices)))
     else:
-        check(L.mc_init(n_gpus, 0))
+        check(L.mc_init(n_gpus, flags))
     _initialised = True
     return L.mc_device_count()
 

@@ -690,15 +690,19 @@ def test_multi_device_split_equals_one_device(gpu, oracle):
     try:
         assert E.init(devices=[0]) == 1
         one = everything()
-        assert E.init() == torch.cuda.device_count()
+        assert E.init() == torch.cuda.device_count() and E.lib().mc_collective() == 0
         many = everything()
+        # the same with the counts summed by one ncclAllReduce per device inside the library (MC_INIT_NCCL)
+        assert E.init(flags=E.INIT_NCCL) == torch.cuda.device_count() and E.lib().mc_collective() == 1
+        nccl = everything()
     finally:
         E.init()
-    for a, b in zip(one, many):
-        if isinstance(a, np.ndarray):
-            assert np.array_equal(a, b)
-        else:
-            assert a == b
+    for other in (many, nccl):
+        for a, b in zip(one, other):
+            if isinstance(a, np.ndarray):
+                assert np.array_equal(a, b)
+            else:
+                assert a == b
 
 
 def test_equity_ranges_vs_oracle(gpu, oracle):
