@@ -208,6 +208,19 @@ int  mc_equity_mc_ev_dev(const uint64_t *hole_masks /* host */, int n_seats, uin
 int  mc_equity_ranges(const int32_t *weight_a /* 1326 */, const int32_t *weight_b /* 1326 */, uint64_t board_mask,
                       uint64_t dead_mask, int64_t wtl[3], int64_t *total /* nullable */);
 
+/* ---- Monte Carlo with a weighted hole range per seat ------------------------------------------------- */
+/* Seat s is fixed (hole_masks[s] != 0) or ranged: weights[s * 1326 + hole index], 0..32767 (the rows of fixed seats are
+ * ignored; holes that hold a board, dead or fixed card are dropped).  Per trial every ranged seat draws a hole exactly in
+ * proportion to its weight (integer alias table, counter-based Philox: trial t depends only on (seed, t), so any split of
+ * the trial range sums to the same counts); trials whose holes collide are dealt again, so the joint law is the product of
+ * the weights restricted to disjoint holes; the missing community cards are uniform.  *n_void (nullable) = trials in
+ * which 4096 attempts all collided (ranges that cannot be dealt together); they are in none of win / tie / loss.
+ * What an equity query of a client with beliefs about its opponents asks (README.md:9); stages as deal-stage
+ * gameplay.clj:56-61 (board_mask = the community cards so far). */
+int  mc_equity_mc_ranges(const int32_t *weights /* n_seats * 1326 */, const uint64_t *hole_masks, int n_seats,
+                         uint64_t board_mask, uint64_t dead_mask, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                         int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_void);
+
 /* ---- 169 x 169 preflop matrix (K5) -------------------------------------------------------------- */
 /* class id: x = rank-2; pair 13x+x; suited (hi>lo) 13*hi+lo; offsuit 13*lo+hi.  wtl[a][b] = {win,tie,loss} of a */
 int  mc_preflop_matrix(int64_t *wtl /* 169*169*3 */);

@@ -270,6 +270,22 @@ def equity_ranges(weight_a, weight_b, board_mask=0, dead_mask=0):
     return list(out), tot.value
 
 
+def equity_mc_ranges(weights, hole_masks, board_mask, dead_mask, seed, first_trial, n_trials):
+    """Monte Carlo with a hole range per seat: weights = one list of 1326 ints per seat (None / ignored for a fixed seat),
+    hole_masks[s] != 0 fixes seat s -> (win, tie, loss, void trials)"""
+    E.ensure_init()
+    n = len(hole_masks)
+    w = np.zeros((max(n, 1), 1326), dtype=np.int32)
+    for s in range(n):
+        if weights[s] is not None:
+            w[s] = np.asarray(weights[s], dtype=np.int32)
+    h = (C.c_uint64 * max(n, 1))(*hole_masks)
+    wi, ti, lo = _seat_arrays(n)
+    void = C.c_uint64(0)
+    E.check(E.lib().mc_equity_mc_ranges(w.ctypes.data, h, n, board_mask, dead_mask, seed, first_trial, n_trials, wi, ti, lo, C.byref(void)))
+    return list(wi[:n]), list(ti[:n]), list(lo[:n]), void.value
+
+
 def preflop_cells(cells):
     E.ensure_init()
     n = len(cells)

@@ -52,6 +52,7 @@ struct DevCtx {
     unsigned long long *h_small = nullptr;        // pinned mirror (mapped)
     unsigned long long *hd_small = nullptr;       // the device's address of h_small
     Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
+    RangeEntry *d_range = nullptr;                // alias tables of mc_equity_mc_ranges: MC_MAX_SEATS x 1326 entries
     long long *d_wtl = nullptr;
     PfBoard *d_pb_boards = nullptr; size_t pb_board_cap = 0;            // config 5 by boards: board list, scratch, win matrix
     uint32_t *d_pb_scratch = nullptr;
@@ -71,6 +72,7 @@ struct DevCtx {
         if (d_small) cudaFree(d_small);
         if (h_small) cudaFreeHost(h_small);
         if (d_matchups) cudaFree(d_matchups);
+        if (d_range) cudaFree(d_range);
         if (d_wtl) cudaFree(d_wtl);
         if (d_pb_boards) cudaFree(d_pb_boards);
         if (d_pb_scratch) cudaFree(d_pb_scratch);
@@ -950,6 +952,88 @@ int mc_equity_mc(const uint64_t *hole_masks, int n_seats, uint64_t board_mask, u
         if (tie) tie[s] = (int64_t)sum[9 + s];
         if (loss) loss[s] = (int64_t)sum[18 + s];
     }
+    return MC_OK;
+}
+
+// ---- Monte Carlo with a range per seat (deal spec R1) ----------------------------------------------------
+namespace {
+// integer alias table (Vose, two stacks filled in ascending index order -- the order is part of the deal spec, the CPU
+// oracle builds the same table): slot i keeps thr[i] of its capacity W for its own hole, the rest belongs to alias[i]
+void build_alias(const std::vector<uint32_t> &w, uint32_t W, RangeEntry *e) {
+    const size_t n = w.size();
+    std::vector<uint64_t> mass(n);
+    std::vector<int> small, large;
+    for (size_t i = 0; i < n; i++) { mass[i] = (uint64_t)w[i] * n; (mass[i] < W ? small : large).push_back((int)i); }
+    while (!small.empty() && !large.empty()) {
+        const int s = small.back(), l = large.back();
+        small.pop_back(); large.pop_back();
+        e[s].thr = (uint32_t)mass[s]; e[s].alias = (uint16_t)l;
+        mass[l] -= (uint64_t)W - mass[s];
+        (mass[l] < W ? small : large).push_back(l);
+    }
+    for (int l : large) { e[l].thr = W; e[l].alias = (uint16_t)l; }
+    for (int s : small) { e[s].thr = W; e[s].alias = (uint16_t)s; }
+}
+}  // namespace
+
+int mc_equity_mc_ranges(const int32_t *weights, const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                        uint64_t seed, uint64_t first_trial, uint64_t n_trials,
+                        int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_void) {
+    if (!weights || !hole_masks) return fail(MC_ERR_INVALID, "null argument");
+    if (n_seats < 1 || n_seats > MC_MAX_SEATS) return fail(MC_ERR_INVALID, "n_seats must be 1..9");
+    if ((board_mask & ~DECK_MASK) || (dead_mask & ~DECK_MASK) || (board_mask & dead_mask)) return fail(MC_ERR_INVALID, "bad board / dead mask");
+    if (__builtin_popcountll(board_mask) > 5) return fail(MC_ERR_INVALID, "more than 5 community cards");
+    McRangeArgs a;
+    std::memset(&a, 0, sizeof a);
+    a.board = board_mask; a.n_seats = n_seats;
+    uint64_t used0 = board_mask | dead_mask;
+    for (int s = 0; s < n_seats; s++) if (hole_masks[s]) {
+        const uint64_t h = hole_masks[s];
+        if ((h & ~DECK_MASK) || __builtin_popcountll(h) != 2) return fail(MC_ERR_INVALID, "a hole mask must hold exactly two of the 52 cards");
+        if (h & used0) return fail(MC_ERR_INVALID, "a card is used twice");
+        used0 |= h; a.hole[s] = h;
+    }
+    a.used0 = used0;
+    std::vector<RangeEntry> entries;
+    int n_ranged = 0;
+    for (int s = 0; s < n_seats; s++) {
+        if (hole_masks[s]) continue;
+        std::vector<uint32_t> w;
+        const size_t off = entries.size();
+        uint64_t W = 0;
+        for (int c1 = 1, idx = 0; c1 < 52; c1++)
+            for (int c0 = 0; c0 < c1; c0++, idx++) {
+                const int32_t wt = weights[(size_t)s * MC_N_HOLES + idx];
+                if (wt < 0 || wt > 32767) return fail(MC_ERR_INVALID, "weights must be 0..32767");
+                const uint64_t h = mc_card_bit(c0) | mc_card_bit(c1);
+                if (wt == 0 || (h & used0)) continue;
+                RangeEntry e{};
+                e.c0 = (unsigned char)__builtin_ctzll(mc_card_bit(c0)); e.c1 = (unsigned char)__builtin_ctzll(mc_card_bit(c1));
+                entries.push_back(e);
+                w.push_back((uint32_t)wt); W += (uint32_t)wt;
+            }
+        if (w.empty()) return fail(MC_ERR_INVALID, "a ranged seat has no hole left (every weighted hole holds a board, dead or fixed card)");
+        build_alias(w, (uint32_t)W, entries.data() + off);
+        a.rs[s] = RangeSeat{(uint32_t)off, (uint32_t)w.size(), (uint32_t)W, (uint32_t)((1ull << 32) % w.size()), (uint32_t)((1ull << 32) % W)};
+        n_ranged++;
+    }
+    for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used0) >> b) & 1ull) a.live[a.n_live++] = (unsigned char)b;
+    if ((int)a.n_live < 5 - __builtin_popcountll(board_mask) + 2 * n_ranged) return fail(MC_ERR_INVALID, "not enough live cards");
+    a.zone_live = (uint32_t)((1ull << 32) % a.n_live);
+    unsigned long long sum[28];
+    int rc = sharded_small_job(n_trials, 28, sum, [&](DevCtx &c, uint64_t lo, uint64_t cnt) -> int {
+        if (!c.d_range) CU(cudaMalloc(&c.d_range, (size_t)MC_MAX_SEATS * MC_N_HOLES * sizeof(RangeEntry)));
+        if (!entries.empty()) CU(cudaMemcpyAsync(c.d_range, entries.data(), entries.size() * sizeof(RangeEntry), cudaMemcpyHostToDevice, c.stream));
+        CU(launch_equity_mc_ranges(a, c.d_range, seed, first_trial + lo, cnt, reinterpret_cast<long long *>(c.d_small), c.tb, c.info, c.stream));
+        return MC_OK;
+    });
+    if (rc) return rc;
+    for (int s = 0; s < n_seats; s++) {
+        if (win) win[s] = (int64_t)sum[s];
+        if (tie) tie[s] = (int64_t)sum[9 + s];
+        if (loss) loss[s] = (int64_t)sum[18 + s];
+    }
+    if (n_void) *n_void = sum[27];
     return MC_OK;
 }
 

@@ -58,6 +58,24 @@ constexpr int SMALL_TICKET_WORD = 126;           // last 64-bit word of the 64-w
 cudaError_t launch_showdown(const EquityArgs &a, uint32_t *d_out, uint32_t ticket, cudaStream_t st);
 cudaError_t launch_eval_one(uint64_t mask, uint32_t *d_out, uint32_t ticket, cudaStream_t st);
 
+// Monte Carlo with a weighted hole range per seat (deal spec R1, DESIGN.md "Ranges per seat").  Alias-table entry of
+// one hole of a seat's list: its two cards (bit positions), the slot it shares its capacity with, and how much of the
+// capacity W is its own.
+struct RangeEntry { unsigned char c0, c1; uint16_t alias; uint32_t thr; };
+struct RangeSeat { uint32_t off, n, W, zone_n, zone_W; };      // entries [off, off + n); zone_x = 2^32 mod x (Lemire)
+struct McRangeArgs {
+    uint64_t hole[MAX_SEATS];        // fixed seats; 0 = ranged
+    RangeSeat rs[MAX_SEATS];         // n = 0 for a fixed seat
+    uint64_t board, used0;           // known community cards; board | dead | fixed holes
+    unsigned char live[52];          // bit positions of the cards outside used0, ascending
+    uint32_t n_live, zone_live;
+    int n_seats;
+};
+constexpr int RANGE_MAX_ATTEMPTS = 4096;
+// d_counts: win[9] tie[9] loss[9] void (28 int64, accumulated into)
+cudaError_t launch_equity_mc_ranges(const McRangeArgs &a, const RangeEntry *d_entries, uint64_t seed, uint64_t first_trial,
+                                    uint64_t n_trials, long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st);
+
 // preflop matrix: matchup list = (hole_a, hole_b, cell index, weight); each block takes matchups
 struct Matchup { uint64_t hole_a, hole_b; int32_t cell_ab, cell_ba; int64_t weight; };
 

@@ -1084,4 +1084,140 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
     return cudaSuccess;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Monte Carlo with a weighted hole range per seat ("hand ranges per seat (weights), which is what an AI
+// client of this server would query", README.md:9; stage states of deal-stage gameplay.clj:56-61).  Deal spec R1:
+// per trial and attempt a word stream Philox(key = seed, ctr = (trial_lo, trial_hi, block | attempt << 16, "MCR1")); a
+// ranged seat draws a slot and a share of the slot's capacity (both exactly uniform: Lemire's bounded sampler, a word in
+// its rejection zone is drawn again) from its integer alias table, i.e. a hole exactly in proportion to its weight; a hole
+// that hits a card already out fails the attempt, which restarts with attempt + 1 (so the joint law is the product of the
+// weights restricted to disjoint holes); the missing community cards are uniform draws from the live list, a card that
+// is already out being drawn again.  Trial t depends only on (seed, t).  One thread per trial, everything in registers;
+// the alias tables (8 B per hole, up to 95 KB) are read from global memory (L2), the hash image from shared memory.
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t TAG_RANGE = 0x4D435231u;
+constexpr int MCR_THREADS = 512;
+struct WordStream {
+    uint32_t k0, k1, c0, c1, c2, w[4];
+    int pos;
+    __device__ __forceinline__ void init(uint32_t seed_lo, uint32_t seed_hi, uint64_t trial, uint32_t attempt) {
+        k0 = seed_lo; k1 = seed_hi; c0 = (uint32_t)trial; c1 = (uint32_t)(trial >> 32); c2 = attempt << 16; pos = 4;
+    }
+    __device__ __forceinline__ uint32_t next() {
+        if (pos == 4) { philox4x32_10(c0, c1, c2, TAG_RANGE, k0, k1, w); c2++; pos = 0; }
+        const uint32_t v = pos == 0 ? w[0] : (pos == 1 ? w[1] : (pos == 2 ? w[2] : w[3]));
+        pos++;
+        return v;
+    }
+    __device__ __forceinline__ uint32_t below(uint32_t n, uint32_t zone) {       // exactly uniform in [0, n)
+        for (;;) {
+            const uint32_t u = next();
+            const uint32_t lo = u * n;
+            if (lo >= zone) return __umulhi(u, n);
+        }
+    }
+};
+
+__global__ void __launch_bounds__(MCR_THREADS, 1)
+equity_mc_ranges_kernel(const __grid_constant__ McRangeArgs a, const RangeEntry *__restrict__ entries, uint32_t seed_lo, uint32_t seed_hi,
+                        uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
+                        long long *__restrict__ d_counts) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    __shared__ CardKey scard[64];
+    __shared__ unsigned char slive[52];
+    __shared__ unsigned long long sred[20];
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
+    if (threadIdx.x < 64) scard[threadIdx.x] = g_card[threadIdx.x];
+    if (threadIdx.x < 52) slive[threadIdx.x] = a.live[threadIdx.x];
+    if (threadIdx.x < 20) sred[threadIdx.x] = 0ull;
+    stage.wait();
+    const uint32_t tbl = staged_table_base(H);
+
+    // hand state of the known community cards
+    HandState base{0, SN_BIAS, (uint32_t)a.board, (uint32_t)(a.board >> 32)};
+    {
+        uint64_t x = a.board;
+        while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; base.t += scard[p].rk; base.sn += scard[p].sn; }
+    }
+    const int need = 5 - __popcll(a.board), n_seats = a.n_seats;
+    Tally<MAX_SEATS> tl; tl.clear();
+    uint32_t voids = 0;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t tr = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; tr < count; tr += nthreads) {
+        const uint64_t trial = first + tr;
+        uint64_t hole[MAX_SEATS], used = 0, bm = 0;
+        bool dealt = false;
+        for (uint32_t attempt = 0; attempt < (uint32_t)RANGE_MAX_ATTEMPTS && !dealt; attempt++) {
+            WordStream ws; ws.init(seed_lo, seed_hi, trial, attempt);
+            used = a.used0;
+            bool fail = false;
+#pragma unroll
+            for (int s = 0; s < MAX_SEATS; s++) {
+                if (s < n_seats && !fail) {
+                    hole[s] = a.hole[s];
+                    if (a.rs[s].n) {
+                        const uint32_t slot = ws.below(a.rs[s].n, a.rs[s].zone_n), vv = ws.below(a.rs[s].W, a.rs[s].zone_W);
+                        RangeEntry e = entries[a.rs[s].off + slot];
+                        if (vv >= e.thr) e = entries[a.rs[s].off + e.alias];
+                        const uint64_t h = (1ull << e.c0) | (1ull << e.c1);
+                        fail = (h & used) != 0ull;
+                        used |= h; hole[s] = h;
+                    }
+                }
+            }
+            if (fail) continue;
+            bm = a.board;
+            for (int k = 0; k < need; k++) {
+                for (;;) {
+                    const uint64_t bit = 1ull << slive[ws.below(a.n_live, a.zone_live)];
+                    if (!(used & bit)) { used |= bit; bm |= bit; break; }
+                }
+            }
+            dealt = true;
+        }
+        if (!dealt) { voids++; continue; }
+        // the board of this trial, then the seats
+        HandState b = base;
+        {
+            uint64_t x = bm & ~a.board;
+            while (x) { const int p = __ffsll((long long)x) - 1; x &= x - 1; b.t += scard[p].rk; b.sn += scard[p].sn; }
+            b.mlo = (uint32_t)bm; b.mhi = (uint32_t)(bm >> 32);
+        }
+        uint32_t key[MAX_SEATS];
+#pragma unroll
+        for (int s = 0; s < MAX_SEATS; s++) {
+            key[s] = 0;
+            if (s < n_seats) {
+                const uint64_t h = hole[s];
+                const int p1 = __ffsll((long long)h) - 1, p2 = 63 - __clzll((long long)h);
+                key[s] = hb_class(b.t + scard[p1].rk + scard[p2].rk, b.sn + scard[p1].sn + scard[p2].sn,
+                                  b.mlo | (uint32_t)h, b.mhi | (uint32_t)(h >> 32), tbl);
+            }
+        }
+        tl.add(key, n_seats);
+    }
+    const uint32_t v = warp_sum(voids);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&sred[19], (unsigned long long)v);
+    tl.flush(n_seats, sred, d_counts);                     // (synchronises the block)
+    if (threadIdx.x == 0 && sred[19]) atomicAdd(reinterpret_cast<unsigned long long *>(d_counts) + 27, sred[19]);
+}
+
+cudaError_t launch_equity_mc_ranges(const McRangeArgs &a, const RangeEntry *d_entries, uint64_t seed, uint64_t first_trial,
+                                    uint64_t n_trials, long long *d_counts, const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
+    if (n_trials == 0) return cudaSuccess;
+    const size_t smem = sizeof(HashBlob);
+    cudaError_t e = cudaFuncSetAttribute(equity_mc_ranges_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    uint64_t want = (n_trials + MCR_THREADS - 1) / MCR_THREADS;
+    const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
+    // (the per-thread counters are 32-bit: one launch covers at most 2^31 trials per thread-slot; the caller's trial
+    // counts are far below grid * threads * 2^31)
+    equity_mc_ranges_kernel<<<grid, MCR_THREADS, smem, st>>>(a, d_entries, (uint32_t)seed, (uint32_t)(seed >> 32), first_trial, n_trials,
+                                                            tb.d_blob, tb.d_card, d_counts);
+    return cudaGetLastError();
+}
+
 }  // namespace mcp

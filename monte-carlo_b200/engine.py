@@ -26,7 +26,7 @@ EXPORTS = [
     "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_end_game", "mc_random_hands", "mc_random_hands_dev",
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
-    "mc_equity_mc", "mc_equity_mc_dev", "mc_equity_exhaustive_ev", "mc_equity_mc_ev", "mc_equity_mc_ev_dev", "mc_equity_ranges", "mc_preflop_matrix", "mc_preflop_matrix_part", "mc_preflop_cells",
+    "mc_equity_mc", "mc_equity_mc_dev", "mc_equity_exhaustive_ev", "mc_equity_mc_ev", "mc_equity_mc_ev_dev", "mc_equity_ranges", "mc_equity_mc_ranges", "mc_preflop_matrix", "mc_preflop_matrix_part", "mc_preflop_cells",
     "mc_preflop_boards_count", "mc_preflop_wins_by_boards", "mc_preflop_matrix_from_wins", "mc_preflop_matrix_by_boards",
     "mc_alloc_host", "mc_free_host",
 ]
@@ -98,6 +98,7 @@ def lib():
     L.mc_equity_exhaustive_ev.argtypes = [P(u64), C.c_int, u64, u64, P(i64), P(i32), P(u32), C.c_int, P(i64), P(i64), P(i64), P(i64), P(u64)]
     L.mc_equity_mc_ev.argtypes = [P(u64), C.c_int, u64, u64, u64, u64, u64, P(i64), P(i32), P(u32), C.c_int, P(i64), P(i64), P(i64), P(i64)]
     L.mc_equity_mc_ev_dev.argtypes = [P(u64), C.c_int, u64, u64, u64, u64, u64, P(i64), P(i32), P(u32), C.c_int, vp, vp]
+    L.mc_equity_mc_ranges.argtypes = [vp, P(u64), C.c_int, u64, u64, u64, u64, u64, P(i64), P(i64), P(i64), P(u64)]
     L.mc_equity_ranges.argtypes = [P(i32), P(i32), u64, u64, P(i64), P(i64)]
     L.mc_preflop_matrix.argtypes = [vp]
     L.mc_preflop_matrix_part.argtypes = [C.c_int, C.c_int, vp, P(i32)]

@@ -121,6 +121,13 @@ int  orc_equity_mc_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_ma
                       const long long *pot_bet, const int *pot_n, const unsigned *pot_players, int n_pots,
                       int64_t *win, int64_t *tie, int64_t *loss, int64_t *chips);
 
+/* Monte Carlo with a weighted hole range per seat (deal spec R1): weights = n_seats x 1326 by hole index
+ * c0 + c1*(c1-1)/2 over card ids (rows of fixed seats are ignored); hole_masks[s] != 0 fixes seat s.  *n_void = trials in
+ * which no attempt dealt disjoint holes (counted in none of win / tie / loss). */
+int  orc_equity_mc_ranges(const int32_t *weights, const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                          uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
+                          int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_void);
+
 /* one cell of the 169x169 preflop matrix (class ids: see include/mcpoker.h) by brute force */
 int  orc_preflop_cell(int class_a, int class_b, int threads, int64_t wtl[3]);
 

@@ -547,6 +547,130 @@ int orc_equity_mc_ev(const uint64_t *hole_masks, int n_seats, uint64_t board_mas
 }
 
 /* ---------------------------------------------------------------------------------------------- */
+/* Monte Carlo with a weighted hole RANGE per seat (SURVEY 8f.3 tail; deal spec R1).  A seat is fixed (hole mask)
+ * or ranged (1326 weights by hole index c0 + c1*(c1-1)/2 over card ids).  used0 = board | dead | fixed holes; a ranged
+ * seat's list = its holes of non-zero weight that avoid used0, in ascending hole index; drawn through an integer alias
+ * table (exactly proportional to the weights); a hole that hits a card already dealt in the trial fails the ATTEMPT, which
+ * is then restarted with the next Philox attempt number (so the joint law is prod_s w_s(h_s) restricted to disjoint holes);
+ * the missing community cards are drawn uniformly from the live cards, re-drawing a card that is already out. */
+#define TAG_RANGE 0x4D435231u
+#define RANGE_MAX_ATTEMPTS 4096
+typedef struct { unsigned char c0, c1; uint16_t alias; uint32_t thr; } range_entry;
+typedef struct { uint32_t key[2], ctr[4], w[4]; int pos; } word_stream;
+static void ws_init(word_stream *st, uint64_t seed, uint64_t trial, uint32_t attempt) {
+    st->key[0] = (uint32_t)seed; st->key[1] = (uint32_t)(seed >> 32);
+    st->ctr[0] = (uint32_t)trial; st->ctr[1] = (uint32_t)(trial >> 32); st->ctr[2] = attempt << 16; st->ctr[3] = TAG_RANGE;
+    st->pos = 4;
+}
+static uint32_t ws_next(word_stream *st) {
+    if (st->pos == 4) { orc_philox4x32_10(st->ctr, st->key, st->w); st->ctr[2]++; st->pos = 0; }
+    return st->w[st->pos++];
+}
+static uint32_t ws_below(word_stream *st, uint32_t n) {          /* exactly uniform in [0, n): Lemire, re-drawing the word */
+    const uint32_t zone = (uint32_t)((1ULL << 32) % n);
+    for (;;) {
+        const uint64_t x = (uint64_t)ws_next(st) * n;
+        if ((uint32_t)x >= zone) return (uint32_t)(x >> 32);
+    }
+}
+/* integer alias table over n items of weights w (sum W): slot i keeps thr[i] of its capacity W for itself, the rest goes to
+ * alias[i].  Vose's construction with two stacks filled in ascending index order (part of the spec: the GPU library
+ * builds the same table). */
+static void build_alias(const uint32_t *w, int n, uint32_t W, range_entry *e) {
+    uint64_t *mass = malloc(sizeof(uint64_t) * (size_t)n);
+    int *small = malloc(sizeof(int) * (size_t)n), *large = malloc(sizeof(int) * (size_t)n), ns = 0, nl = 0;
+    for (int i = 0; i < n; i++) { mass[i] = (uint64_t)w[i] * (uint64_t)n; if (mass[i] < W) small[ns++] = i; else large[nl++] = i; }
+    while (ns && nl) {
+        const int s_ = small[--ns], l = large[--nl];
+        e[s_].thr = (uint32_t)mass[s_]; e[s_].alias = (uint16_t)l;
+        mass[l] -= (uint64_t)W - mass[s_];
+        if (mass[l] < W) small[ns++] = l; else large[nl++] = l;
+    }
+    while (nl) { const int l = large[--nl]; e[l].thr = W; e[l].alias = (uint16_t)l; }
+    while (ns) { const int s_ = small[--ns]; e[s_].thr = W; e[s_].alias = (uint16_t)s_; }     /* (only by rounding: never with integers) */
+    free(mass); free(small); free(large);
+}
+int orc_equity_mc_ranges(const int32_t *weights, const uint64_t *hole_masks, int n_seats, uint64_t board_mask, uint64_t dead_mask,
+                         uint64_t seed, uint64_t first_trial, uint64_t n_trials, int threads,
+                         int64_t *win, int64_t *tie, int64_t *loss, uint64_t *n_void) {
+    if (n_seats < 1 || n_seats > 9) return -1;
+    if ((board_mask & ~DECK_MASK) || (dead_mask & ~DECK_MASK) || (board_mask & dead_mask) || __builtin_popcountll(board_mask) > 5) return -1;
+    cards_init();
+    uint64_t used0 = board_mask | dead_mask;
+    for (int s = 0; s < n_seats; s++) if (hole_masks[s]) {
+        if ((hole_masks[s] & ~DECK_MASK) || __builtin_popcountll(hole_masks[s]) != 2 || (hole_masks[s] & used0)) return -1;
+        used0 |= hole_masks[s];
+    }
+    range_entry *tab[9] = {0}; uint32_t n_of[9] = {0}, W_of[9] = {0};
+    int rc = 0, n_ranged = 0;
+    for (int s = 0; s < n_seats && !rc; s++) if (!hole_masks[s]) {
+        uint32_t w[1326]; range_entry *e = malloc(sizeof(range_entry) * 1326); int n = 0; uint64_t W = 0;
+        tab[s] = e;
+        for (int c1 = 1, idx = 0; c1 < 52; c1++) for (int c0 = 0; c0 < c1; c0++, idx++) {
+            const int32_t wt = weights[s * 1326 + idx];
+            if (wt < 0 || wt > 32767) rc = -1;
+            if (wt <= 0 || ((CARD_BIT[c0] | CARD_BIT[c1]) & used0)) continue;
+            e[n].c0 = (unsigned char)__builtin_ctzll(CARD_BIT[c0]); e[n].c1 = (unsigned char)__builtin_ctzll(CARD_BIT[c1]);
+            w[n++] = (uint32_t)wt; W += (uint32_t)wt;
+        }
+        if (n == 0) rc = -1;
+        if (!rc) { build_alias(w, n, (uint32_t)W, e); n_of[s] = (uint32_t)n; W_of[s] = (uint32_t)W; n_ranged++; }
+    }
+    int live[52], n_live = 0;
+    for (int b = 0; b < 64; b++) if (((DECK_MASK & ~used0) >> b) & 1ULL) live[n_live++] = b;
+    const int need = 5 - __builtin_popcountll(board_mask);
+    if (!rc && n_live < need + 2 * n_ranged) rc = -1;
+    int64_t W_[9] = {0}, T_[9] = {0}, L_[9] = {0}; uint64_t V_ = 0;
+    if (!rc) {
+        int nt = use_threads(threads);
+        (void)nt;
+#pragma omp parallel num_threads(nt)
+        {
+            int64_t w[9] = {0}, t_[9] = {0}, l[9] = {0}; uint64_t v = 0;
+#pragma omp for schedule(static)
+            for (long long i = 0; i < (long long)n_trials; i++) {
+                const uint64_t trial = first_trial + (uint64_t)i;
+                uint64_t holes[9], bm = 0; int ok = 0;
+                for (uint32_t attempt = 0; attempt < RANGE_MAX_ATTEMPTS && !ok; attempt++) {
+                    word_stream st; ws_init(&st, seed, trial, attempt);
+                    uint64_t used = used0; int fail = 0;
+                    for (int s = 0; s < n_seats && !fail; s++) {
+                        holes[s] = hole_masks[s];
+                        if (hole_masks[s]) continue;
+                        const uint32_t slot = ws_below(&st, n_of[s]), vv = ws_below(&st, W_of[s]);
+                        const range_entry *e = &tab[s][slot];
+                        if (vv >= e->thr) e = &tab[s][e->alias];
+                        const uint64_t h = (1ULL << e->c0) | (1ULL << e->c1);
+                        if (h & used) { fail = 1; break; }
+                        used |= h; holes[s] = h;
+                    }
+                    if (fail) continue;
+                    bm = board_mask;
+                    for (int k = 0; k < need; k++) {
+                        for (;;) {
+                            const uint64_t bit = 1ULL << live[ws_below(&st, (uint32_t)n_live)];
+                            if (!(used & bit)) { used |= bit; bm |= bit; break; }
+                        }
+                    }
+                    ok = 1;
+                }
+                if (!ok) { v++; continue; }
+                uint32_t keys[9];
+                for (int s = 0; s < n_seats; s++) keys[s] = orc_eval_mask(bm | holes[s]);
+                count_showdown(keys, n_seats, w, t_, l);
+            }
+#pragma omp critical
+            { for (int s = 0; s < 9; s++) { W_[s] += w[s]; T_[s] += t_[s]; L_[s] += l[s]; } V_ += v; }
+        }
+    }
+    for (int s = 0; s < 9; s++) free(tab[s]);
+    if (rc) return rc;
+    for (int s = 0; s < n_seats; s++) { win[s] = W_[s]; tie[s] = T_[s]; loss[s] = L_[s]; }
+    if (n_void) *n_void = V_;
+    return 0;
+}
+
+/* ---------------------------------------------------------------------------------------------- */
 /* 169 starting-hand classes: x = rank-2 (0..12); pair 13x+x; suited hi>lo 13*hi+lo; offsuit 13*lo+hi */
 static int class_holes(int cls, uint64_t *out) {
     int a = cls / 13, b = cls % 13, n = 0;

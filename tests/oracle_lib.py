@@ -194,6 +194,25 @@ def equity_mc_ev(holes, pots, board, dead, seed, first, n_trials, threads=0):
     return rc, list(w), list(t), list(l), list(ch)
 
 
+def equity_mc_ranges(weights, holes, board, dead, seed, first, n_trials, threads=0):
+    """weights: one list of 1326 ints per seat (None for a fixed seat) -> (rc, win, tie, loss, void)"""
+    import numpy as np
+    n = len(holes)
+    w = np.zeros((n, 1326), dtype=np.int32)
+    for s in range(n):
+        if weights[s] is not None:
+            w[s] = np.asarray(weights[s], dtype=np.int32)
+    h = (C.c_uint64 * n)(*holes)
+    wi, ti, lo = (C.c_int64 * n)(), (C.c_int64 * n)(), (C.c_int64 * n)()
+    void = C.c_uint64(0)
+    L = lib()
+    L.orc_equity_mc_ranges.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64,
+                                       C.c_uint64, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                       C.POINTER(C.c_uint64)]
+    rc = L.orc_equity_mc_ranges(w.ctypes.data, h, n, board, dead, seed, first, n_trials, threads, wi, ti, lo, C.byref(void))
+    return rc, list(wi), list(ti), list(lo), void.value
+
+
 def philox(ctr, key):
     c, k, o = (C.c_uint32 * 4)(*ctr), (C.c_uint32 * 2)(*key), (C.c_uint32 * 4)()
     lib().orc_philox4x32_10(c, k, o)

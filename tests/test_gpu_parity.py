@@ -613,6 +613,65 @@ def test_equity_ev_monte_carlo_vs_oracle(gpu, oracle):
     assert api.equity_mc_ev(holes, pots, 0, 0, SEED, 0, 1 << 18) == (w, t, l, ch)
 
 
+def test_equity_mc_ranges_vs_oracle(gpu, oracle):
+    """SURVEY 8f.3 tail: Monte Carlo with a weighted hole range per seat (deal spec R1) -- bit-exact against the oracle's
+    restatement of the spec for 1..9 seats, mixed fixed / ranged seats, preflop to river, narrow ranges that collide
+    often, dead cards; split invariance; heads-up within 4 sigma of the exhaustive range-vs-range call; void trials"""
+    api = gpu.api
+    rng = random.Random(41)
+    holes = [(a, b) for b in range(52) for a in range(b)]
+    for n_seats in (1, 2, 3, 6, 9):
+        for case in range(3):
+            n_known = rng.choice([0, 3, 4, 5])
+            n_fixed = rng.randint(0, n_seats - 1) if case else 0
+            ids = rng.sample(range(52), 2 * n_fixed + n_known + 2)
+            fixed_at = set(rng.sample(range(n_seats), n_fixed))
+            hm, weights, k = [], [], 0
+            for s in range(n_seats):
+                if s in fixed_at:
+                    hm.append(api.mask_of_ids(ids[2 * k:2 * k + 2]))
+                    weights.append(None)
+                    k += 1
+                else:
+                    hm.append(0)
+                    w = [0] * 1326
+                    for a, b in rng.sample(holes, rng.choice([3, 20, 200, 1326])):
+                        w[api.hole_index(a, b)] = rng.randint(1, 32767 if case == 2 else 9)
+                    weights.append(w)
+            board = api.mask_of_ids(ids[2 * n_fixed:2 * n_fixed + n_known])
+            dead = api.mask_of_ids(ids[-2:]) if rng.random() < 0.5 else 0
+            seed, first, n = rng.getrandbits(64), rng.getrandbits(40), 20_000
+            rc, w, t, l, void = oracle.equity_mc_ranges(weights, hm, board, dead, seed, first, n)
+            if rc != 0:                                             # a range emptied by the known cards
+                with pytest.raises(gpu.engine.McError):
+                    api.equity_mc_ranges(weights, hm, board, dead, seed, first, n)
+                continue
+            got = api.equity_mc_ranges(weights, hm, board, dead, seed, first, n)
+            assert got == (w, t, l, void), (n_seats, case, n_known, n_fixed)
+            assert all(a + b + c + void == n for a, b, c in zip(w, t, l))
+    # heads-up: Monte Carlo against the exact weighted equity of mc_equity_ranges, split invariance
+    wa, wb = [0] * 1326, [0] * 1326
+    for a, b in rng.sample(holes, 40):
+        wa[api.hole_index(a, b)] = rng.randint(1, 9)
+    for a, b in rng.sample(holes, 40):
+        wb[api.hole_index(a, b)] = rng.randint(1, 9)
+    board = api.mask_of_ids([3, 17, 44])
+    exact, total = api.equity_ranges(wa, wb, board, 0)
+    n = 1 << 22
+    w, t, l, void = api.equity_mc_ranges([wa, wb], [0, 0], board, 0, 99, 0, n)
+    assert void == 0 and w[0] == l[1] and t[0] == t[1]
+    p = exact[0] / total
+    assert abs(w[0] / n - p) < 4 * (p * (1 - p) / n) ** 0.5
+    a = api.equity_mc_ranges([wa, wb], [0, 0], board, 0, 99, 0, 1_000_001)
+    b = api.equity_mc_ranges([wa, wb], [0, 0], board, 0, 99, 1_000_001, n - 1_000_001)
+    assert [x + y for x, y in zip(a[0], b[0])] == w and a[3] + b[3] == void
+    # two ranges that can never be dealt together: every trial is void
+    only, other = [0] * 1326, [0] * 1326
+    only[api.hole_index(12, 25)] = 3
+    other[api.hole_index(12, 38)] = 1
+    assert api.equity_mc_ranges([only, other], [0, 0], 0, 0, 1, 0, 300) == ([0, 0], [0, 0], [0, 0], 300)
+
+
 def test_lifecycle_is_safe_against_calls_in_flight(gpu, oracle):
     """the header's promise: mc_init* / mc_shutdown wait for calls in flight and calls never run on a context that is
     being torn down.  Four threads hammer compute calls (batch, single-hand ticket path, equity) while a fifth cycles

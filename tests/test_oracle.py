@@ -267,3 +267,53 @@ def test_ev_settlement_conserves_chips_when_shares_divide(oracle):
     rc, w2, t2, l2 = oracle.equity_mc([aa, 0, 0], 0, 0, 9, 0, 5000)
     assert (w, t, l) == (w2, t2, l2)
     assert oracle.equity_exhaustive_ev([aa, kk], [(10, 2, [])])[0] == -1           # a pot nobody plays for: the reference divides by zero
+
+
+def _hole_index(a, b):
+    a, b = min(a, b), max(a, b)
+    return a + b * (b - 1) // 2
+
+
+def test_mc_ranges_oracle_matches_exhaustive_and_voids(oracle):
+    """deal spec R1 on the CPU: heads-up weighted ranges by Monte Carlo within 4 sigma of the exact weighted equity
+    (orc_equity_exhaustive over every disjoint hole pair); ranges that can never be dealt together are all void"""
+    import random
+    rnd = random.Random(5)
+    board = oracle.card_bit(3) | oracle.card_bit(17) | oracle.card_bit(44)
+    holes = [(a, b) for b in range(52) for a in range(b)]
+    wa, wb = [0] * 1326, [0] * 1326
+    for a, b in rnd.sample(holes, 12):
+        wa[_hole_index(a, b)] = rnd.randint(1, 5)
+    for a, b in rnd.sample(holes, 12):
+        wb[_hole_index(a, b)] = rnd.randint(1, 5)
+    num, den = 0.0, 0.0
+    for a, b in holes:
+        for c, d in holes:
+            w = wa[_hole_index(a, b)] * wb[_hole_index(c, d)]
+            ha, hb = oracle.card_bit(a) | oracle.card_bit(b), oracle.card_bit(c) | oracle.card_bit(d)
+            if not w or (ha & hb) or ((ha | hb) & board):
+                continue
+            rc, wi, ti, lo, nb = oracle.equity_exhaustive([ha, hb], board, 0, threads=1)
+            num += w * wi[0] / nb
+            den += w
+    p = num / den
+    n = 400_000
+    rc, wi, ti, lo, void = oracle.equity_mc_ranges([wa, wb], [0, 0], board, 0, 77, 0, n)
+    assert rc == 0 and void == 0 and wi[0] + ti[0] + lo[0] == n and wi[0] == lo[1] and ti[0] == ti[1]
+    assert abs(wi[0] / n - p) < 4 * (p * (1 - p) / n) ** 0.5
+    # split invariance: trial t depends only on (seed, t)
+    a = oracle.equity_mc_ranges([wa, wb], [0, 0], board, 0, 77, 0, 1000)
+    b = oracle.equity_mc_ranges([wa, wb], [0, 0], board, 0, 77, 1000, 2000)
+    c = oracle.equity_mc_ranges([wa, wb], [0, 0], board, 0, 77, 0, 3000)
+    assert [x + y for x, y in zip(a[1], b[1])] == c[1]
+    # both seats can only hold the ace of hearts: every attempt collides
+    only = [0] * 1326
+    only[_hole_index(12, 25)] = 3
+    other = [0] * 1326
+    other[_hole_index(12, 38)] = 1
+    rc, wi, ti, lo, void = oracle.equity_mc_ranges([only, other], [0, 0], 0, 0, 1, 0, 50)
+    assert rc == 0 and void == 50 and wi == [0, 0] and ti == [0, 0] and lo == [0, 0]
+    # a fixed seat beside a ranged one; a range emptied by the board is an error
+    rc, wi, ti, lo, void = oracle.equity_mc_ranges([None, wb], [oracle.card_bit(12) | oracle.card_bit(25), 0], board, 0, 3, 0, 2000)
+    assert rc == 0 and wi[0] + ti[0] + lo[0] == 2000
+    assert oracle.equity_mc_ranges([only, wb], [0, 0], oracle.card_bit(12) | oracle.card_bit(1) | oracle.card_bit(2), 0, 1, 0, 10)[0] == -1
