@@ -2,6 +2,7 @@
 // warp reductions, the per-seat showdown counters and their block-level flush into 64-bit global counts.
 #pragma once
 #include <cstdint>
+#include <cstdio>
 #include "kernels.cuh"
 
 namespace mcp {
@@ -77,9 +78,24 @@ struct BulkStage {
 // Loads from a staged (read-only) shared-memory table by 32-bit shared address.  Plain asm, so the compiler may
 // schedule them freely; u16 entries arrive zero-extended in a full register (a C++ uint16_t load is kept as a
 // 16-bit value and merged / masked with extra PRMT and LOP3 around every select or compare).
-__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
-__device__ __forceinline__ uint2 lds_u32x2(uint32_t addr) { uint2 v; asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr)); return v; }
-__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+// MCP_CHECK build (make check -> libmcpoker_check.so; compute-sanitizer is closed on the GPU pool): every table load
+// verifies that its bytes lie inside the block's shared-memory allocation and are naturally aligned, and traps otherwise.
+#ifdef MCP_CHECK
+__device__ __forceinline__ void lds_check(uint32_t addr, uint32_t bytes) {
+    uint32_t total;
+    asm("mov.u32 %0, %%total_smem_size;" : "=r"(total));
+    if (addr + bytes > total || (addr & (bytes - 1u))) {
+        printf("MCP_CHECK: shared load of %u bytes at %u outside the %u-byte allocation or misaligned (block %d thread %d)\n",
+               bytes, addr, total, (int)blockIdx.x, (int)threadIdx.x);
+        __trap();
+    }
+}
+#else
+__device__ __forceinline__ void lds_check(uint32_t, uint32_t) {}
+#endif
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) { lds_check(addr, 4); uint32_t v; asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+__device__ __forceinline__ uint2 lds_u32x2(uint32_t addr) { lds_check(addr, 8); uint2 v; asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr)); return v; }
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) { lds_check(addr, 2); uint32_t v; asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
 // shared address of a table, to be taken AFTER BulkStage::wait(): every lds_* through it depends on this volatile
 // asm, so none can move above the wait, and the compiler keeps the base in a register instead of rebuilding it
 __device__ __forceinline__ uint32_t staged_table_base(const void *smem_table) {

@@ -6,7 +6,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmcpoker.so")
+LIB_PATH = os.environ.get("MCP_LIB_PATH") or os.path.join(_HERE, "libmcpoker.so")       # (MCP_LIB_PATH: the checked build)
 CSRC = os.path.join(_HERE, "csrc")
 
 MC_OK, MC_ERR_INVALID, MC_ERR_NOT_INIT, MC_ERR_CUDA, MC_ERR_NO_DEVICE, MC_ERR_TOO_FEW = 0, -1, -2, -3, -4, -5
