@@ -157,11 +157,19 @@ __device__ __forceinline__ void chips_fold_warp(const uint32_t (&chips)[NSLOT], 
 static void make_pot_params(const PotArgs *pots, const int *seat_of, int n_kernel_seats, PotParams *pp) {
     memset(pp, 0, sizeof *pp);
     if (!pots) return;
-    pp->n_pots = pots->n_pots;
+    // pots played for by the same seats have the same winners: they share one slot, whose share table is the sum of
+    // theirs (floor(a / k) + floor(b / k), each pot truncated on its own as update-stacks does)
     uint64_t sum = 0;
+    uint32_t mask_of[MAX_POTS];
     for (int p = 0; p < pots->n_pots; p++) {
-        for (int q = 0; q < n_kernel_seats; q++) pp->in[p][q] = ((pots->players[p] >> seat_of[q]) & 1u) ? 0x1FFFFu : 0u;
-        for (int k = 1; k <= MAX_SEATS; k++) pp->share[p][k] = pots->total[p] / (uint32_t)k;
+        int slot = 0;
+        while (slot < pp->n_pots && mask_of[slot] != pots->players[p]) slot++;
+        if (slot == pp->n_pots) {
+            mask_of[slot] = pots->players[p];
+            for (int q = 0; q < n_kernel_seats; q++) pp->in[slot][q] = ((pots->players[p] >> seat_of[q]) & 1u) ? 0x1FFFFu : 0u;
+            pp->n_pots++;
+        }
+        for (int k = 1; k <= MAX_SEATS; k++) pp->share[slot][k] += pots->total[p] / (uint32_t)k;
         sum += pots->total[p];
     }
     const uint64_t f = sum ? 0xFFFFFFFFull / sum : 0xFFFFFFFFull;
@@ -1003,12 +1011,17 @@ static cudaError_t launch_mc(const McFyParams &prm, const DeviceTables &tb, long
     return launch_mc_nfx<NR, MC_THREADS, NF_ALL>(prm, tb, d_counts, grid, st);
 }
 
-// EV variant: the general seat shape only, one block size per number of random seats (the nine chip accumulators cost
-// registers: 96 x 640 threads where the plain kernel runs 80 x 768; up to three random seats 80 x 768 instead of 64 x 1024)
-template <int NR> constexpr int mc_ev_threads() { return NR <= 3 ? 768 : 640; }
+// EV variant: the general seat shape only
+// 768 threads (the chip accumulators then squeeze the kernel into 80 registers, at most 16 bytes of spill) or, with
+// MCP_K4_EV_THREADS=640, 640 threads x 96 registers (A/B arm)
+static int mc_ev_threads(int nr) {
+    static const bool t640 = [] { const char *e = getenv("MCP_K4_EV_THREADS"); return e && atoi(e) == 640; }();
+    return (t640 && nr >= 4) ? 640 : 768;
+}
 template <int NR>
 static cudaError_t launch_mc_ev(const McFyParams &prm, const DeviceTables &tb, long long *d_counts, int grid, cudaStream_t st) {
-    return launch_mc_nfx<NR, mc_ev_threads<NR>(), MAX_SEATS - NR, true>(prm, tb, d_counts, grid, st);
+    if constexpr (NR >= 4) { if (mc_ev_threads(NR) == 640) return launch_mc_nfx<NR, 640, MAX_SEATS - NR, true>(prm, tb, d_counts, grid, st); }
+    return launch_mc_nfx<NR, 768, MAX_SEATS - NR, true>(prm, tb, d_counts, grid, st);
 }
 
 cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t first_trial, uint64_t n_trials,
@@ -1043,7 +1056,7 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
     const bool ev = pots && pots->n_pots > 0;
     make_pot_params(ev ? pots : nullptr, prm.seat_of, a.n_seats, &prm.pots);
     const int grid = di.sm_count;
-    const int MC_THREADS = ev ? (nr <= 3 ? 768 : 640) : mc_threads(nr);
+    const int MC_THREADS = ev ? mc_ev_threads(nr) : mc_threads(nr);
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves
     for (uint64_t done = 0; done < n_trials; done += per_launch) {
         prm.first = first_trial + done;

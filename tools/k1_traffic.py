@@ -14,7 +14,8 @@ import bench  # noqa: E402
 
 rep = sys.argv[1]
 log2 = int(sys.argv[2]) if len(sys.argv) > 2 else 28
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+# an .ncu-rep, or the CSV `ncu -i rep --page raw --csv` made of it on the GPU box (reports do not fit gpurun_out/)
+raw = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units = rows[0], rows[1]
 col = {h: i for i, h in enumerate(hdr)}
@@ -27,7 +28,7 @@ def to_bytes(v, u):
 best = None
 for r in rows[2:]:
     name = r[col["Kernel Name"]]
-    if "eval_stream_hash_kernel" in name and "Lay7" in name and "unsigned int" in name:
+    if "eval_stream_hash_kernel<6, " in name and "Lay7, unsigned int>" in name:
         rd = to_bytes(r[col["dram__bytes_read.sum"]], units[col["dram__bytes_read.sum"]])
         wr = to_bytes(r[col["dram__bytes_write.sum"]], units[col["dram__bytes_write.sum"]])
         best = (name, rd, wr)                      # the last launch of the capture
