@@ -190,6 +190,18 @@ def colex_ranks_dev(torch, masks):
     return rank.to(torch.int32)
 
 
+def pack27_dev(torch, ranks):
+    """int32 colex ranks on the device (a multiple of 32 of them) -> the 27-bit stream of mc_eval_batch_colex27 (int32 words)"""
+    r = ranks.to(torch.int64).reshape(-1, 32)
+    out = torch.zeros((r.shape[0], 28), dtype=torch.int64, device=ranks.device)
+    for j in range(32):
+        w, sh = (27 * j) >> 5, (27 * j) & 31
+        v = r[:, j] << sh
+        out[:, w] |= v & 0xFFFFFFFF
+        out[:, w + 1] |= v >> 32
+    return out[:, :27].to(torch.int32).reshape(-1)      # (values >= 2^31 wrap to the same 32 bits)
+
+
 def timed_region(torch, dist, world, fn, steps, warmup):
     """W untimed + K timed calls of fn(), CUDA events on the current stream, barrier + synchronize on both
     sides, max over ranks.  returns total milliseconds of the K steps."""
@@ -332,7 +344,8 @@ def run_ours(args):
 
     # ---- e2e: the host-buffer C-ABI calls, pinned memory, H2D + kernels + D2H inside the timed region ----
     # Three wire formats of the same batch call, all bound by the host link:
-    #   colex32   4 B in (colex rank of the 7 cards) + 2 B out (class id)      mc_eval_batch_colex32   <- the headline e2e
+    #   colex27   3.375 B in (the same ranks as a 27-bit stream) + 2 B out     mc_eval_batch_colex27   <- the headline e2e
+    #   colex32   4 B in (colex rank of the 7 cards) + 2 B out (class id)      mc_eval_batch_colex32
     #   packed48  6 B in (seven 6-bit card positions) + 4 B out (nibble key)   mc_eval_batch_packed48
     #   mask      8 B in (card mask) + 4 B out                                 mc_eval7_batch
     # The compact inputs are produced on the device here (bit shuffling only) and land in pinned host memory before the
@@ -347,6 +360,9 @@ def run_ours(args):
     h_ranks = torch.empty(ne, dtype=torch.int32).pin_memory()
     h_ranks.copy_(colex_ranks_dev(torch, masks[:ne]))
     h_cls = torch.empty(ne, dtype=torch.int16).pin_memory()
+    h_s27 = torch.empty(27 * ne // 32, dtype=torch.int32).pin_memory()
+    h_s27.copy_(pack27_dev(torch, colex_ranks_dev(torch, masks[:ne])))
+    h_cls27 = torch.empty(ne, dtype=torch.int16).pin_memory()
     torch.cuda.synchronize()
     e2e_steps = max(2, args.steps // 2)
 
@@ -358,6 +374,9 @@ def run_ours(args):
 
     def e2e32_step():
         E.check(L.mc_eval_batch_colex32(h_ranks.data_ptr(), ne, h_cls.data_ptr()))
+
+    def e2e27_step():
+        E.check(L.mc_eval_batch_colex27(h_s27.data_ptr(), ne, h_cls27.data_ptr()))
 
     e2e_ms = wall_region(torch, dist, world, e2e_step, e2e_steps, 1)
     e2e_value = world * ne * e2e_steps / (e2e_ms * 1e-3)
@@ -372,6 +391,10 @@ def run_ours(args):
     class_keys = torch.from_numpy(api.class_keys().astype(np.int64)).to(torch.int32)
     if not torch.equal(class_keys[h_cls.long() & 0xFFFF], h_keys):
         raise SystemExit("colex32 class ids differ from the mask call's keys")
+    e2e27_ms = wall_region(torch, dist, world, e2e27_step, e2e_steps, 2)
+    e2e27_value = world * ne * e2e_steps / (e2e27_ms * 1e-3)
+    if not torch.equal(h_cls27, h_cls):
+        raise SystemExit("colex27 class ids differ from the colex32 call's")
     # the same call on pageable buffers (what a caller gets without mc_alloc_host / pinning)
     pg_masks, pg_keys = h_masks.numpy().copy(), np.empty(ne, dtype=np.uint32)
     E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
@@ -379,39 +402,47 @@ def run_ours(args):
     E.check(L.mc_eval7_batch(pg_masks.ctypes.data, ne, pg_keys.ctypes.data))
     pageable_value = ne / (time.perf_counter() - t0)
     del pg_masks, pg_keys
-    # The host link alone, measured as a ceiling for ALL ranks at once: every rank copies the same pinned buffers at
-    # the same time (barrier + synchronize on both sides, max over ranks), nothing else running: H2D alone, D2H alone,
-    # and both directions together at the byte ratio of the colex32 call (4 in : 2 out) on two streams.
+    # The host link alone, measured as a ceiling for ALL ranks at once: every rank copies the headline call's pinned buffers
+    # (27-bit stream in, class ids out) at the same time, in the pipeline's own 4 Mi-hand pieces on two streams, nothing
+    # else running (barrier + synchronize on both sides, max over ranks): H2D alone, D2H alone, both directions together.
     s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-    d_ranks, d_cls = torch.empty(ne, dtype=torch.int32, device="cuda"), torch.empty(ne, dtype=torch.int16, device="cuda")
+    d_s27, d_cls = torch.empty(27 * ne // 32, dtype=torch.int32, device="cuda"), torch.empty(ne, dtype=torch.int16, device="cuda")
+    piece = min(ne, 1 << 22)
 
     def copy_h2d():
         with torch.cuda.stream(s_in):
-            d_ranks.copy_(h_ranks, non_blocking=True)
+            for lo in range(0, ne, piece):
+                a, b = 27 * lo // 32, 27 * (lo + piece) // 32
+                d_s27[a:b].copy_(h_s27[a:b], non_blocking=True)
 
     def copy_d2h():
         with torch.cuda.stream(s_out):
-            h_cls.copy_(d_cls, non_blocking=True)
+            for lo in range(0, ne, piece):
+                h_cls27[lo:lo + piece].copy_(d_cls[lo:lo + piece], non_blocking=True)
 
     def copy_both():
         copy_h2d()
         copy_d2h()
 
     reps = 4
-    h2d_gbs = world * 4 * ne * reps / (wall_region(torch, dist, world, copy_h2d, reps, 1) * 1e-3) / 1e9
-    d2h_gbs = world * 2 * ne * reps / (wall_region(torch, dist, world, copy_d2h, reps, 1) * 1e-3) / 1e9
+    in_b, out_b = 27 / 8, 2
+    h2d_gbs = world * in_b * ne * reps / (wall_region(torch, dist, world, copy_h2d, reps, 1) * 1e-3) / 1e9
+    d2h_gbs = world * out_b * ne * reps / (wall_region(torch, dist, world, copy_d2h, reps, 1) * 1e-3) / 1e9
     both_ms = wall_region(torch, dist, world, copy_both, reps, 1)
     both_evals = world * ne * reps / (both_ms * 1e-3)               # hands/s if the copies were all there is to do
     link = {"all_ranks_at_once": True, "h2d_alone_gbs_total": h2d_gbs, "d2h_alone_gbs_total": d2h_gbs,
-            "h2d_while_d2h_gbs_total": 4 * both_evals / 1e9, "d2h_while_h2d_gbs_total": 2 * both_evals / 1e9,
-            "ceiling_evals_per_s": both_evals,
-            "ceiling_note": "bare cudaMemcpyAsync of the colex32 call's buffers (4 B in + 2 B out per hand, both directions at "
-                            "once, every rank at the same time, nothing else running): what the host link of this box allows",
-            "colex32_frac_of_ceiling": e2e32_value / both_evals,
-            "colex32_h2d_gbs_total": 4 * e2e32_value / 1e9, "colex32_d2h_gbs_total": 2 * e2e32_value / 1e9,
+            "h2d_while_d2h_gbs_total": in_b * both_evals / 1e9, "d2h_while_h2d_gbs_total": out_b * both_evals / 1e9,
+            "bare_copies_evals_per_s": both_evals,
+            "bare_copies_note": "bare cudaMemcpyAsync of the colex27 call's buffers (3.375 B in + 2 B out per hand) in 4 Mi-hand pieces, both "
+                                "directions at once, every rank at the same time, nothing else running: what the host link of this box "
+                                "delivers to plain copies (the pipelined call can come out slightly above it: three streams keep more "
+                                "copies queued than the two of this leg)",
+            "colex27_frac_of_bare_copies": e2e27_value / both_evals,
+            "colex27_h2d_gbs_total": in_b * e2e27_value / 1e9, "colex27_d2h_gbs_total": out_b * e2e27_value / 1e9,
+            "colex32_h2d_gbs_total": 4 * e2e32_value / 1e9,
             "packed48_h2d_gbs_total": 6 * e2e48_value / 1e9, "mask_h2d_gbs_total": 8 * e2e_value / 1e9,
             "pageable_buffers_evals_per_s_per_gpu": pageable_value}
-    del masks, keys, d_ranks, d_cls
+    del masks, keys, d_s27, d_cls
 
     # ---- integer pipes of this GPU, measured in this run: thread-ops per clock per SM ----------------
     pipes = None
@@ -676,10 +707,12 @@ def run_ours(args):
                          "frac": achieved_gbs / hbm_peak, "traffic": traffic, "traffic_source": traffic_note, "peak_source": peak_src,
                          "kernel": "eval_stream_hash_kernel<6, Lay7, uint32_t>", "algorithmic_bytes_per_eval": ALGO_BYTES_PER_EVAL,
                          "int_issue_frac": (value / world) * OPS["eval"] / int_peak, "ops_per_eval": OPS["eval"]},
-            "e2e": {"value": e2e32_value, "unit": "evals/s", "h2d_bytes_per_step": 4 * ne, "d2h_bytes_per_step": 2 * ne,
+            "e2e": {"value": e2e27_value, "unit": "evals/s", "h2d_bytes_per_step": 27 * ne // 8, "d2h_bytes_per_step": 2 * ne,
                     "hands_per_step": ne,
-                    "call": "mc_eval_batch_colex32 (pinned host buffers; 4-byte colex ranks in, 2-byte class ids out; 3-stage "
-                            "copy / unrank / K1 / copy pipeline); values checked equal to the mask call's keys in this run",
+                    "call": "mc_eval_batch_colex27 (pinned host buffers; colex ranks as a 27-bit stream in, 2-byte class ids out; 3-stage "
+                            "copy / unrank / K1 / copy pipeline); values checked equal to the colex32 and mask calls' in this run",
+                    "colex32_call": {"value": e2e32_value, "h2d_bytes_per_step": 4 * ne, "d2h_bytes_per_step": 2 * ne,
+                                     "call": "mc_eval_batch_colex32 (4-byte colex ranks in, 2-byte class ids out)"},
                     "packed48_call": {"value": e2e48_value, "h2d_bytes_per_step": 6 * ne, "d2h_bytes_per_step": 4 * ne,
                                       "call": "mc_eval_batch_packed48 (6-byte hands in, 4-byte nibble keys out)"},
                     "mask_call": {"value": e2e_value, "h2d_bytes_per_step": 8 * ne, "d2h_bytes_per_step": 4 * ne,

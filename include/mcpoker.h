@@ -71,6 +71,7 @@ extern "C" {
 #define MC_IN_MASK64        0   /* uint64 card masks, 8 B per hand (5..7 cards) */
 #define MC_IN_PACKED48      1   /* seven 6-bit card positions, 6 B per hand (5..7 cards) */
 #define MC_IN_COLEX32       2   /* uint32 colex rank of a 7-card hand over card ids, 4 B per hand */
+#define MC_IN_COLEX27       3   /* the same ranks as a bit stream, 27 bits per hand: 32 hands in 27 words, 3.375 B per hand */
 
 #define MC_MAX_SEATS        9
 #define MC_MAX_POTS         8   /* side pots of the EV calls */
@@ -110,6 +111,9 @@ int  mc_eval_batch_packed48(const uint8_t *hands /* 6*n bytes */, size_t n, uint
  * (the combination index of mc_enumerate7_range; < C(52,7) = 133,784,560 < 2^27) in, its class id out: 4 B + 2 B per hand
  * over the host link instead of 8 + 4.  A rank >= C(52,7) gives MC_CLASS_INVALID.  Unranked on the device. */
 int  mc_eval_batch_colex32(const uint32_t *ranks, size_t n, uint16_t *classes);
+/* The same with the ranks packed: a little-endian bit stream of 27 bits per hand (C(52,7) < 2^27), hand j = bits
+ * [27 j, 27 j + 27) of the stream, i.e. 32 hands in 27 uint32 words; `stream` holds ceil(27 n / 32) words. */
+int  mc_eval_batch_colex27(const uint32_t *stream, size_t n, uint16_t *classes);
 /* Every combination of the above: in_format MC_IN_*, key_format MC_KEY_* (out = uint32 keys, or uint16 class ids for
  * MC_KEY_CLASS16).  stage_cards: 5, 6 or 7 = the batch is flop / turn / river hands, 0 = decide from the first hand; it
  * only selects the kernel's table image -- hands of another size are still evaluated exactly, just slower. */

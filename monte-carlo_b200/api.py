@@ -113,6 +113,38 @@ def colex_rank(masks):
     return rank.astype(np.uint32)
 
 
+def pack27(ranks):
+    """uint32 colex ranks (< 2^27) -> the 27-bit little-endian bit stream of mc_eval_batch_colex27 (uint32 words,
+    ceil(27 n / 32) of them): hand j occupies bits [27 j, 27 j + 27)"""
+    r = np.ascontiguousarray(ranks, dtype=np.uint32)
+    if np.any(r >> np.uint32(27)):
+        raise ValueError("a rank does not fit 27 bits")
+    n = r.shape[0]
+    groups = (n + 31) // 32
+    pad = np.zeros(groups * 32, dtype=np.uint64)
+    pad[:n] = r
+    pad = pad.reshape(groups, 32)
+    out = np.zeros((groups, 28), dtype=np.uint64)                      # (word 27 only catches the shifted-out zeros)
+    for j in range(32):
+        w, sh = (27 * j) >> 5, (27 * j) & 31
+        v = pad[:, j] << np.uint64(sh)
+        out[:, w] |= v & np.uint64(0xFFFFFFFF)
+        out[:, w + 1] |= v >> np.uint64(32)
+    words = out[:, :27].astype(np.uint32).reshape(-1)
+    return np.ascontiguousarray(words[:(27 * n + 31) // 32])
+
+
+def eval_batch_colex27(stream, n, out=None):
+    """the 27-bit stream of n hands (pack27) -> uint16 class ids"""
+    E.ensure_init()
+    stream = np.ascontiguousarray(stream, dtype=np.uint32)
+    if stream.shape[0] < (27 * n + 31) // 32:
+        raise ValueError("the stream is shorter than ceil(27 n / 32) words")
+    cls = out if out is not None else np.empty(n, dtype=np.uint16)
+    E.check(E.lib().mc_eval_batch_colex27(stream.ctypes.data, n, cls.ctypes.data))
+    return cls
+
+
 def eval_batch_colex32(ranks, out=None):
     """uint32 colex ranks of 7-card hands -> uint16 class ids (class_keys()[id] = nibble key)"""
     E.ensure_init()
@@ -126,7 +158,7 @@ def eval_batch(hands, in_format, key_format=E.KEY_NIBBLE, stage_cards=0):
     """any wire format in (IN_MASK64 uint64, IN_PACKED48 6 bytes, IN_COLEX32 uint32), keys (uint32) or class ids
     (uint16, KEY_CLASS16) out"""
     E.ensure_init()
-    fmt = {E.IN_MASK64: (np.uint64, 1), E.IN_PACKED48: (np.uint8, 6), E.IN_COLEX32: (np.uint32, 1)}.get(in_format)
+    fmt = {E.IN_MASK64: (np.uint64, 1), E.IN_PACKED48: (np.uint8, 6), E.IN_COLEX32: (np.uint32, 1)}.get(in_format)      # (colex27: eval_batch_colex27)
     hands = np.ascontiguousarray(hands, dtype=fmt[0]) if fmt else np.ascontiguousarray(hands)   # (an unknown format is the library's to refuse)
     n = hands.size // (fmt[1] if fmt else 1)
     out = np.empty(n, dtype=np.uint16 if key_format == E.KEY_CLASS16 else np.uint32)

@@ -535,11 +535,16 @@ size_t stage_hands() {        // hands per pipeline stage of the host-buffer cal
     }();
     return v;
 }
-size_t wire_bytes(int in_format) { return in_format == MC_IN_MASK64 ? 8 : in_format == MC_IN_PACKED48 ? 6 : 4; }
+// bytes of the first `hands` hands of a batch in the wire format (colex27: whole 32-bit words of the bit stream; the
+// pipeline cuts batches at multiples of 32 hands, where the stream is word-aligned)
+size_t wire_bytes(int in_format, size_t hands) {
+    if (in_format == MC_IN_COLEX27) return 4 * ((27 * hands + 31) / 32);
+    return hands * (in_format == MC_IN_MASK64 ? 8 : in_format == MC_IN_PACKED48 ? 6 : 4);
+}
 // how many cards the FIRST hand of a host batch holds (the host-buffer calls pick the K1 image by it; hands of another
 // size are still evaluated exactly, on the kernel's slow path)
 int first_hand_cards(const unsigned char *src, int in_format) {
-    if (in_format == MC_IN_COLEX32) return 7;
+    if (in_format == MC_IN_COLEX32 || in_format == MC_IN_COLEX27) return 7;
     uint64_t h = 0;
     std::memcpy(&h, src, in_format == MC_IN_MASK64 ? 8 : 6);
     if (in_format == MC_IN_MASK64) return __builtin_popcountll(h);
@@ -554,9 +559,10 @@ int first_hand_cards(const unsigned char *src, int in_format) {
 int eval_batch_pipeline(const unsigned char *src, int in_format, size_t n, unsigned char *dst, int key_format, int stage_cards) {
     int rc;
     const int nd = (int)g_ctx.size();
-    const size_t in_bytes = wire_bytes(in_format), out_bytes = key_format == MC_KEY_CLASS16 ? 2 : 4;
-    // slices start on even hands: the staging buffers keep the alignment of the two-hand loads / stores
-    const size_t per_dev = ((n + nd - 1) / nd + 1) & ~(size_t)1;
+    const size_t out_bytes = key_format == MC_KEY_CLASS16 ? 2 : 4;
+    // slices start at multiples of 32 hands: there the 27-bit stream is word-aligned (and every format keeps the alignment
+    // of the two-hand loads / stores)
+    const size_t per_dev = ((n + nd - 1) / nd + 31) & ~(size_t)31;
     std::vector<size_t> pos(nd), end(nd);
     for (int d = 0; d < nd; d++) {
         pos[d] = std::min(n, per_dev * d); end[d] = std::min(n, pos[d] + per_dev);
@@ -576,12 +582,14 @@ int eval_batch_pipeline(const unsigned char *src, int in_format, size_t n, unsig
             const int s = (int)(round % N_SLOTS);
             const size_t cnt = std::min(stage_hands(), end[d] - pos[d]);
             CU(cudaSetDevice(c.device));
+            const size_t in_off = wire_bytes(in_format, pos[d]), in_len = wire_bytes(in_format, pos[d] + cnt) - in_off;
             if (in_format == MC_IN_MASK64) {
-                CU(cudaMemcpyAsync(c.d_in[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
+                CU(cudaMemcpyAsync(c.d_in[s], src + in_off, in_len, cudaMemcpyHostToDevice, c.slot_stream[s]));
             } else {
-                CU(cudaMemcpyAsync(c.d_pk[s], src + pos[d] * in_bytes, cnt * in_bytes, cudaMemcpyHostToDevice, c.slot_stream[s]));
+                CU(cudaMemcpyAsync(c.d_pk[s], src + in_off, in_len, cudaMemcpyHostToDevice, c.slot_stream[s]));
                 if (in_format == MC_IN_PACKED48) CU(launch_unpack48(c.d_pk[s], cnt, c.d_in[s], c.info, c.slot_stream[s]));
-                else CU(launch_unrank_colex32(reinterpret_cast<const uint32_t *>(c.d_pk[s]), cnt, c.d_in[s], c.info, c.slot_stream[s]));
+                else if (in_format == MC_IN_COLEX32) CU(launch_unrank_colex32(reinterpret_cast<const uint32_t *>(c.d_pk[s]), cnt, c.d_in[s], c.info, c.slot_stream[s]));
+                else CU(launch_unrank_colex27(reinterpret_cast<const uint32_t *>(c.d_pk[s]), cnt, c.d_in[s], c.info, c.slot_stream[s]));
             }
             CU(launch_k1(c.d_in[s], cnt, c.d_out[s], key_format, stage_cards, c.info, &c.tb, c.slot_stream[s]));
             CU(cudaMemcpyAsync(dst + pos[d] * out_bytes, c.d_out[s], cnt * out_bytes, cudaMemcpyDeviceToHost, c.slot_stream[s]));
@@ -598,7 +606,7 @@ int eval_batch_pipeline(const unsigned char *src, int in_format, size_t n, unsig
     return MC_OK;
 }
 int eval_batch_host(const void *in, int in_format, size_t n, void *out, int key_format, int stage_cards) {
-    if (in_format < MC_IN_MASK64 || in_format > MC_IN_COLEX32) return fail(MC_ERR_INVALID, "unknown input format");
+    if (in_format < MC_IN_MASK64 || in_format > MC_IN_COLEX27) return fail(MC_ERR_INVALID, "unknown input format");
     if (!key_format_ok(key_format)) return fail(MC_ERR_INVALID, "unknown key format");
     Use use;
     if (use.rc) return use.rc;
@@ -625,6 +633,9 @@ int mc_eval_batch_packed48(const uint8_t *hands, size_t n, uint32_t *keys) {
 }
 int mc_eval_batch_colex32(const uint32_t *ranks, size_t n, uint16_t *classes) {
     return eval_batch_host(ranks, MC_IN_COLEX32, n, classes, MC_KEY_CLASS16, 7);
+}
+int mc_eval_batch_colex27(const uint32_t *stream, size_t n, uint16_t *classes) {
+    return eval_batch_host(stream, MC_IN_COLEX27, n, classes, MC_KEY_CLASS16, 7);
 }
 void *mc_alloc_host(size_t bytes) {
     Use use;

@@ -368,9 +368,12 @@ cudaError_t launch_unpack48(const unsigned char *d_packed, size_t n, uint64_t *d
 // (six steps each) in a shared table of binomials padded with 0xFFFFFFFF: the largest x with C(x, k) <= rest is
 // automatically below the previous card, so no bound is carried.  A rank >= C(52,7) yields the mask 1 (not a card).
 // ---------------------------------------------------------------------------------------------------
+// colex27: the same ranks as a little-endian bit stream, 27 bits per hand (C(52,7) < 2^27): hand j is bits [27 j, 27 j + 27),
+// so 32 hands travel in 27 words -- 3.375 B per hand.  The stream is read with two 4-byte loads and a funnel shift.
 constexpr int UNR_COLS = 72;
+template <bool PACKED27>
 __global__ void __launch_bounds__(256)
-unrank_colex32_kernel(const uint32_t *__restrict__ ranks, size_t n, uint64_t *__restrict__ masks) {
+unrank_colex_kernel(const uint32_t *__restrict__ ranks, size_t n, uint64_t *__restrict__ masks) {
     __shared__ uint32_t sb[8 * UNR_COLS];                         // sb[k * 72 + x] = C(x, k) for x <= 52, else 2^32 - 1
     for (int i = threadIdx.x; i < 8 * UNR_COLS; i += blockDim.x) {
         const int k = i / UNR_COLS, x = i % UNR_COLS;
@@ -381,7 +384,14 @@ unrank_colex32_kernel(const uint32_t *__restrict__ ranks, size_t n, uint64_t *__
     __syncthreads();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        uint32_t rest = __ldcs(ranks + i);
+        uint32_t rest;
+        if (PACKED27) {
+            const size_t bit = 27 * i, w = bit >> 5;
+            const uint32_t lo = __ldg(ranks + w), hi = ((bit & 31) > 5) ? __ldg(ranks + w + 1) : 0u;   // (the next word only when the field crosses into it)
+            rest = __funnelshift_r(lo, hi, (uint32_t)(bit & 31)) & 0x7FFFFFFu;
+        } else {
+            rest = __ldcs(ranks + i);
+        }
         uint64_t m = 1ull;
         if (rest < cbinom(52, 7)) {
             m = 0ull;
@@ -401,7 +411,13 @@ unrank_colex32_kernel(const uint32_t *__restrict__ ranks, size_t n, uint64_t *__
 cudaError_t launch_unrank_colex32(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     size_t want = (n + 255) / 256, cap = (size_t)di.sm_count * 8;
-    unrank_colex32_kernel<<<(int)(want > cap ? cap : want), 256, 0, st>>>(d_ranks, n, d_masks);
+    unrank_colex_kernel<false><<<(int)(want > cap ? cap : want), 256, 0, st>>>(d_ranks, n, d_masks);
+    return cudaGetLastError();
+}
+cudaError_t launch_unrank_colex27(const uint32_t *d_stream, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    size_t want = (n + 255) / 256, cap = (size_t)di.sm_count * 8;
+    unrank_colex_kernel<true><<<(int)(want > cap ? cap : want), 256, 0, st>>>(d_stream, n, d_masks);
     return cudaGetLastError();
 }
 

@@ -11,7 +11,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 MC_OK, MC_ERR_INVALID, MC_ERR_NOT_INIT, MC_ERR_CUDA, MC_ERR_NO_DEVICE, MC_ERR_TOO_FEW = 0, -1, -2, -3, -4, -5
 KEY_NIBBLE, KEY_PACKED, KEY_NIBBLE_FLO, KEY_NIBBLE_TABLE, KEY_NIBBLE_HASH, KEY_CLASS16 = 0, 1, 2, 3, 4, 5
-IN_MASK64, IN_PACKED48, IN_COLEX32 = 0, 1, 2
+IN_MASK64, IN_PACKED48, IN_COLEX32, IN_COLEX27 = 0, 1, 2, 3
 CLASS_INVALID = 0xFFFF
 N_HAND_CLASSES = 7462
 KEY_INVALID = 0xFFFFFFFF
@@ -22,7 +22,7 @@ EXPORTS = [
     "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version", "mc_collective",
     "mc_card_bit", "mc_key_packed_to_nibble", "mc_key_decode",
     "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval_batch_packed48", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
-    "mc_eval_batch", "mc_eval_batch_colex32", "mc_eval_batch_dev", "mc_unrank_colex32_dev", "mc_class_keys",
+    "mc_eval_batch", "mc_eval_batch_colex32", "mc_eval_batch_colex27", "mc_eval_batch_dev", "mc_unrank_colex32_dev", "mc_class_keys",
     "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_end_game", "mc_random_hands", "mc_random_hands_dev",
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
@@ -81,6 +81,7 @@ def lib():
     L.mc_end_game.argtypes = [u64, P(u64), C.c_int, P(i64), P(i32), P(u32), C.c_int, P(u32), P(i32), P(i32), P(u32), P(i64)]
     L.mc_eval_batch.argtypes = [vp, C.c_int, sz, vp, C.c_int, C.c_int]
     L.mc_eval_batch_colex32.argtypes = [vp, sz, vp]
+    L.mc_eval_batch_colex27.argtypes = [vp, sz, vp]
     L.mc_eval_batch_dev.argtypes = [vp, sz, vp, C.c_int, C.c_int, vp]
     L.mc_unrank_colex32_dev.argtypes = [vp, sz, vp, vp]
     L.mc_class_keys.argtypes = [vp, C.c_int]

@@ -192,8 +192,10 @@ def test_k1_every_seven_card_hand_key_by_key(gpu, oracle):
         masks = oracle.enumerate_masks(7, first, n)
         want = oracle.eval_batch(masks, 0)
         bad += int(np.count_nonzero(gpu.api.eval7_batch(masks) != want))
-        cls = gpu.api.eval_batch_colex32(np.arange(first, first + n, dtype=np.uint32))
+        ranks = np.arange(first, first + n, dtype=np.uint32)
+        cls = gpu.api.eval_batch_colex32(ranks)
         bad_c += int(np.count_nonzero(class_keys[cls] != want))
+        bad_c += int(np.count_nonzero(gpu.api.eval_batch_colex27(gpu.api.pack27(ranks), n) != cls))      # the 27-bit stream
     assert bad == 0 and bad_c == 0
 
 
@@ -242,7 +244,10 @@ def test_eval_batch_every_format_and_stage_hint(gpu, oracle):
     for n in (len(h7), 4097, 33, 3, 2, 1):
         assert np.array_equal(ck[api.eval_batch_colex32(ranks[:n])], want7[:n])
         assert np.array_equal(api.eval_batch(ranks[:n], E.IN_COLEX32, E.KEY_NIBBLE, 7), want7[:n])
+        assert np.array_equal(ck[api.eval_batch_colex27(api.pack27(ranks[:n]), n)], want7[:n])
     assert api.eval_batch_colex32(np.zeros(0, dtype=np.uint32)).shape == (0,)
+    big = np.concatenate([ranks] * 30)                                  # 9 M hands: several pipeline stages of the bit stream
+    assert np.array_equal(api.eval_batch_colex27(api.pack27(big), len(big)), api.eval_batch_colex32(big))
     # ranks past the last combination, invalid masks, the tests' rank-1 hands (no class): MC_CLASS_INVALID / MC_KEY_INVALID
     bad = np.array([133784560, 133784561, 0xFFFFFFFF, 1 << 27], dtype=np.uint32)
     assert np.all(api.eval_batch_colex32(bad) == 0xFFFF)

@@ -74,6 +74,21 @@ def test_colex_rank_wire_format(pkg, oracle):
         pkg.api.colex_rank(oracle.random_hands(7, 0, 10, 6))
 
 
+def test_pack27_wire_format(pkg):
+    """api.pack27: 27 bits per hand, little-endian bit stream; every field reads back, ragged sizes"""
+    import numpy as np
+    rng = np.random.default_rng(3)
+    for n in (1, 31, 32, 33, 1000, 4097):
+        r = rng.integers(0, 133784560, n, dtype=np.uint32)
+        s = pkg.api.pack27(r)
+        assert s.dtype == np.uint32 and s.shape[0] == (27 * n + 31) // 32
+        bits = int.from_bytes(s.tobytes(), "little")
+        back = [(bits >> (27 * j)) & 0x7FFFFFF for j in range(n)]
+        assert back == r.tolist()
+    with pytest.raises(ValueError):
+        pkg.api.pack27(np.array([1 << 27], dtype=np.uint32))
+
+
 def test_no_gpu_means_loud_failure_not_fallback(pkg):
     import torch
     if torch.cuda.is_available():
