@@ -118,6 +118,17 @@ int  mc_eval_batch_colex27(const uint32_t *stream, size_t n, uint16_t *classes);
  * MC_KEY_CLASS16).  stage_cards: 5, 6 or 7 = the batch is flop / turn / river hands, 0 = decide from the first hand; it
  * only selects the kernel's table image -- hands of another size are still evaluated exactly, just slower. */
 int  mc_eval_batch(const void *hands, int in_format, size_t n, void *out, int key_format, int stage_cards);
+/* Allocation-free variant of the colex32 evaluation for callers that cannot allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * d_ranks (uint32 colex ranks) and d_classes (uint16 class ids, 4-byte aligned) are the caller's device
+ * buffers on the current device; the intermediate card masks live in a static device array inside the library
+ * (MC_NOALLOC_MAX_HANDS x 8 B = 8 MiB, held by every GPU that loads the library until the process exits).  The call
+ * allocates nothing and only enqueues two kernels on `stream`.  n > MC_NOALLOC_MAX_HANDS fails with MC_ERR_INVALID.
+ * All calls on a device share the array: calls that overlap on the GPU (different streams, or graph replays in
+ * flight together) race -- serialise them on one stream.  Nothing has to be cleared between calls: each call overwrites
+ * the n entries it reads.  Same results as mc_eval_batch_colex32.  Needs mc_init for the current device. */
+#define MC_NOALLOC_MAX_HANDS 1048576
+int  mc_eval_batch_colex32_dev_noalloc(const uint32_t *d_ranks, size_t n, uint16_t *d_classes, void *stream);
 /* class id -> nibble key, MC_N_HAND_CLASSES entries, ascending (so class ids order like keys).  Needs mc_init. */
 int  mc_class_keys(uint32_t *keys, int n /* = MC_N_HAND_CLASSES */);
 /* Page-locked host memory for the buffers of the host-buffer calls: they copy straight from / into the caller's

@@ -53,6 +53,7 @@ struct DevCtx {
     unsigned long long *hd_small = nullptr;       // the device's address of h_small
     Matchup *d_matchups = nullptr; size_t matchup_cap = 0;
     RangeEntry *d_range = nullptr;                // alias tables of mc_equity_mc_ranges: MC_MAX_SEATS x 1326 entries
+    uint64_t *d_noalloc_masks = nullptr;          // this device's address of the static scratch of the allocation-free call (not owned)
     long long *d_wtl = nullptr;
     PfBoard *d_pb_boards = nullptr; size_t pb_board_cap = 0;            // config 5 by boards: board list, scratch, win matrix
     uint32_t *d_pb_scratch = nullptr;
@@ -249,6 +250,7 @@ int init_devices(const int *ids, int n, unsigned flags) {
         if (!g_tables) { rc = build_tables(*c); if (rc) return rc; }
         rc = upload_tables(*c);
         if (rc) return rc;
+        CU(noalloc_scratch_address(&c->d_noalloc_masks));     // device d is current: the symbol's address on THIS device
         fresh.push_back(std::move(c));
     }
     // the collective, if asked for and if there is anything to reduce over
@@ -516,6 +518,25 @@ int mc_unrank_colex32_dev(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, 
     int rc = current_info(&di);
     if (rc) return rc;
     CU(launch_unrank_colex32(d_ranks, n, d_masks, di, (cudaStream_t)stream));
+    return MC_OK;
+}
+// The allocation-free variant of the colex32 batch evaluation: ranks and class ids in the caller's device memory, the
+// intermediate masks in the library's static device array.  No cudaMalloc / cudaFree / allocating routine on this path.
+int mc_eval_batch_colex32_dev_noalloc(const uint32_t *d_ranks, size_t n, uint16_t *d_classes, void *stream) {
+    if (n > NOALLOC_MAX_HANDS)
+        return fail(MC_ERR_INVALID, "mc_eval_batch_colex32_dev_noalloc: n = " + std::to_string(n) + " exceeds MC_NOALLOC_MAX_HANDS = " +
+                                    std::to_string(NOALLOC_MAX_HANDS) + " (the size of the static scratch); split the batch");
+    if (n && (!d_ranks || !d_classes)) return fail(MC_ERR_INVALID, "null device buffer");
+    if (reinterpret_cast<uintptr_t>(d_classes) & 3) return fail(MC_ERR_INVALID, "d_classes must be 4-byte aligned");
+    std::shared_lock<std::shared_mutex> life(g_life);
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    DevCtx *c = nullptr;
+    for (auto &x : g_ctx) if (x->device == dev) c = x.get();
+    if (!c) return fail(MC_ERR_NOT_INIT, "mc_init / mc_init_devices has not been called for the current device");
+    if (n == 0) return MC_OK;
+    CU(launch_unrank_colex32(d_ranks, n, c->d_noalloc_masks, c->info, (cudaStream_t)stream));
+    CU(launch_eval_stream_hash(c->d_noalloc_masks, n, d_classes, true, 7, c->tb, c->info, (cudaStream_t)stream));
     return MC_OK;
 }
 int mc_class_keys(uint32_t *keys, int n) {

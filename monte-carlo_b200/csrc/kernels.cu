@@ -422,6 +422,25 @@ cudaError_t launch_unrank_colex27(const uint32_t *d_stream, size_t n, uint64_t *
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Scratch of the allocation-free entry point mc_eval_batch_colex32_dev_noalloc (capi.cu): the card masks the colex
+// ranks are unranked into before K1 reads them.  A file-scope array instead of a cudaMalloc'ed stage, so the call can be
+// made where allocation is forbidden (CUDA graph capture, serving loops).  8 MiB; every GPU that loads the library
+// holds it until the process exits.  Every call on a device shares it: calls that overlap on the GPU race.  Nothing in
+// it has to start at zero -- the unranking kernel overwrites the first n entries, which are the only ones K1 reads.
+// In host code `g_noalloc_masks` is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress (below, called once per device at mc_init with that device current).
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long g_noalloc_masks[NOALLOC_MAX_HANDS];
+
+cudaError_t noalloc_scratch_address(uint64_t **d_ptr) {
+    void *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_masks);
+    if (e != cudaSuccess) return e;
+    *d_ptr = static_cast<uint64_t *>(p);
+    return cudaSuccess;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // single showdown: one warp, lane s = seat s (end-game ranking + group-winners, gameplay.clj:118-132)
 // ---------------------------------------------------------------------------------------------------
 __global__ void showdown_kernel(const __grid_constant__ EquityArgs a, uint32_t *__restrict__ out, uint32_t ticket) {

@@ -31,6 +31,10 @@ cudaError_t launch_eval_stream_hash(const uint64_t *d_masks, size_t n, void *d_o
 // colex ranks of 7-card hands over card ids (sum_i C(c_i, i+1), < C(52,7)) -> card masks; a rank out of range gives
 // the mask 1 (not a card), which every K1 variant maps to the invalid key / class
 cudaError_t launch_unrank_colex32(const uint32_t *d_ranks, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st);
+// scratch of the allocation-free colex32 call: a file-scope __device__ array of NOALLOC_MAX_HANDS masks in kernels.cu;
+// its device address on the CURRENT device (cudaGetSymbolAddress; the array's name is not an address in host code)
+constexpr size_t NOALLOC_MAX_HANDS = (size_t)1 << 20;
+cudaError_t noalloc_scratch_address(uint64_t **d_ptr);
 // the same ranks as a 27-bit little-endian bit stream (hand j = bits [27 j, 27 j + 27)); d_stream 4-byte aligned
 cudaError_t launch_unrank_colex27(const uint32_t *d_stream, size_t n, uint64_t *d_masks, const DeviceInfo &di, cudaStream_t st);
 cudaError_t launch_random_hands(uint64_t seed, uint64_t first, size_t n, int n_cards, uint64_t *d_masks,

@@ -14,6 +14,7 @@ KEY_NIBBLE, KEY_PACKED, KEY_NIBBLE_FLO, KEY_NIBBLE_TABLE, KEY_NIBBLE_HASH, KEY_C
 IN_MASK64, IN_PACKED48, IN_COLEX32, IN_COLEX27 = 0, 1, 2, 3
 CLASS_INVALID = 0xFFFF
 N_HAND_CLASSES = 7462
+NOALLOC_MAX_HANDS = 1 << 20
 KEY_INVALID = 0xFFFFFFFF
 MAX_SEATS = 9
 N_CLASSES = 169
@@ -22,7 +23,7 @@ EXPORTS = [
     "mc_init", "mc_init_devices", "mc_shutdown", "mc_device_count", "mc_last_error", "mc_abi_version", "mc_collective",
     "mc_card_bit", "mc_key_packed_to_nibble", "mc_key_decode",
     "mc_eval_cards", "mc_eval7_batch", "mc_eval7_batch_fmt", "mc_eval_batch_packed48", "mc_eval7_batch_dev", "mc_eval7_batch_dev_fmt",
-    "mc_eval_batch", "mc_eval_batch_colex32", "mc_eval_batch_colex27", "mc_eval_batch_dev", "mc_unrank_colex32_dev", "mc_class_keys",
+    "mc_eval_batch", "mc_eval_batch_colex32", "mc_eval_batch_colex27", "mc_eval_batch_colex32_dev_noalloc", "mc_eval_batch_dev", "mc_unrank_colex32_dev", "mc_class_keys",
     "mc_showdown", "mc_showdown_groups", "mc_settle_pots", "mc_end_game", "mc_random_hands", "mc_random_hands_dev",
     "mc_enumerate7", "mc_enumerate7_range", "mc_enumerate7_dev",
     "mc_equity_exhaustive", "mc_equity_exhaustive_range", "mc_equity_exhaustive_dev",
@@ -82,6 +83,7 @@ def lib():
     L.mc_eval_batch.argtypes = [vp, C.c_int, sz, vp, C.c_int, C.c_int]
     L.mc_eval_batch_colex32.argtypes = [vp, sz, vp]
     L.mc_eval_batch_colex27.argtypes = [vp, sz, vp]
+    L.mc_eval_batch_colex32_dev_noalloc.argtypes = [vp, sz, vp, vp]
     L.mc_eval_batch_dev.argtypes = [vp, sz, vp, C.c_int, C.c_int, vp]
     L.mc_unrank_colex32_dev.argtypes = [vp, sz, vp, vp]
     L.mc_class_keys.argtypes = [vp, C.c_int]
