@@ -114,7 +114,8 @@ struct Tally {
 struct PotParams {
     uint32_t in[MAX_POTS][MAX_SEATS];          // by kernel seat
     uint32_t share[MAX_POTS][MAX_SEATS + 1];   // share[p][k] = floor(total / k), k = 1..9
-    int n_pots;
+    uint32_t main_share[MAX_SEATS + 1];        // K4: the pots every seat plays for are settled from the showdown itself
+    int n_pots, has_main;
     uint32_t flush_every;
 };
 template <int NSLOT>
@@ -154,14 +155,22 @@ __device__ __forceinline__ void chips_fold_warp(const uint32_t (&chips)[NSLOT], 
     }
 }
 // host: kernel-seat view of the caller's pots.  seat_of[q] = caller seat of kernel seat q (n_kernel_seats of them)
-static void make_pot_params(const PotArgs *pots, const int *seat_of, int n_kernel_seats, PotParams *pp) {
+// use_main: pots played for by EVERY seat go to main_share instead of a slot (their winners are the showdown's own)
+static void make_pot_params(const PotArgs *pots, const int *seat_of, int n_kernel_seats, PotParams *pp, bool use_main = false) {
     memset(pp, 0, sizeof *pp);
     if (!pots) return;
+    const uint32_t everybody = (1u << n_kernel_seats) - 1u;
     // pots played for by the same seats have the same winners: they share one slot, whose share table is the sum of
     // theirs (floor(a / k) + floor(b / k), each pot truncated on its own as update-stacks does)
     uint64_t sum = 0;
     uint32_t mask_of[MAX_POTS];
     for (int p = 0; p < pots->n_pots; p++) {
+        if (use_main && pots->players[p] == everybody) {
+            for (int k = 1; k <= MAX_SEATS; k++) pp->main_share[k] += pots->total[p] / (uint32_t)k;
+            pp->has_main = 1;
+            sum += pots->total[p];
+            continue;
+        }
         int slot = 0;
         while (slot < pp->n_pots && mask_of[slot] != pots->players[p]) slot++;
         if (slot == pp->n_pots) {
@@ -227,9 +236,7 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
     fill_binom(sbin);
     if (threadIdx.x < LIVE_MAX) slive[threadIdx.x] = prm.live[threadIdx.x];
     if (threadIdx.x < 19 + MAX_SEATS) sred[threadIdx.x] = 0ull;
-    stage.wait();
-    const uint32_t tbl = staged_table_base(H);
-
+    __syncthreads();                     // binomials and live list are in place; the hash image is still on its way
     const int n_seats = prm.n_seats, nl = prm.n_live;
     Tally<NS> tl; tl.clear();
     uint32_t chips[NS], since = 0;
@@ -240,9 +247,12 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
     const uint64_t me = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t lo = me * per < prm.count ? me * per : prm.count;
     const uint64_t hi = lo + per < prm.count ? lo + per : prm.count;
+    // the colex unranking of the thread's first board needs no hash table: it runs while the TMA engine stages the image
+    Walker<K> w;
+    if (lo < hi) w.init((uint32_t)(prm.first + lo), nl, sbin, slive, prm.base);
+    stage.wait();
+    const uint32_t tbl = staged_table_base(H);
     if (lo < hi) {
-        Walker<K> w;
-        w.init((uint32_t)(prm.first + lo), nl, sbin, slive, prm.base);
         for (uint64_t i = lo; i < hi; i++) {
             const HandState b = w.hand();
             uint32_t key[NS];
@@ -956,6 +966,11 @@ equity_mc_fy_kernel(const __grid_constant__ McFyParams prm, const HashBlob *__re
         for (int s = 0; s < NSLOT; s++) if (s < NR || s - NR < nf) acc[s] += at[s] * inc;
         units++;
         if constexpr (EV && NSLOT > 0) {
+            if (prm.pots.has_main) {                     // (uniform) the main pot: its winners are the seats at the maximum
+                const uint32_t share = prm.pots.main_share[nbest];
+#pragma unroll
+                for (int s = 0; s < NSLOT; s++) chips[s] += at[s] * share;
+            }
             pots_settle<NSLOT>(prm.pots, key, chips);
             if (++since == prm.pots.flush_every) { chips_fold_thread<NSLOT>(chips, sred + 20); since = 0; }
         }
@@ -1054,7 +1069,7 @@ cudaError_t launch_equity_mc_fy(const EquityArgs &a, uint64_t seed, uint64_t fir
         prm.thr[w] = (uint32_t)((1ull << 32) % prod);
     }
     const bool ev = pots && pots->n_pots > 0;
-    make_pot_params(ev ? pots : nullptr, prm.seat_of, a.n_seats, &prm.pots);
+    make_pot_params(ev ? pots : nullptr, prm.seat_of, a.n_seats, &prm.pots, true);
     const int grid = di.sm_count;
     const int MC_THREADS = ev ? mc_ev_threads(nr) : mc_threads(nr);
     const uint64_t per_launch = 65535ull * (uint64_t)grid * MC_THREADS;       // 16-bit per-thread counter halves

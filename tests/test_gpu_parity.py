@@ -401,6 +401,31 @@ def test_equity_mc_converges_to_exhaustive(gpu):
     assert abs(w[0] / n - p) < 4 * sigma
 
 
+def test_config4_acceptance_checks(gpu):
+    """BASELINE config 4: 9 seats, seat 0 holds A-A, eight random seats.  (i) seat-0 equity of the bench seed
+    within 4 sigma (binomial) of an independent-seed run; (ii) seats 1-8 are exchangeable, so their win / tie / loss counts
+    agree with one another within 5 sigma of their binomial spread; (iii) every seat's counts add up to the trials;
+    (iv) a trial has exactly one winner or at least two tied seats"""
+    api = gpu.api
+    holes = [api.mask_of_ids([12, 25])] + [0] * 8
+    n = 1 << 26
+    wa, ta, la = api.equity_mc(holes, 0, 0, SEED, 0, n)
+    wb, tb, lb = api.equity_mc(holes, 0, 0, 0xC0FFEE1234, 0, n)
+    for w, t, l in ((wa, ta, la), (wb, tb, lb)):
+        assert all(w[s] + t[s] + l[s] == n for s in range(9))
+        assert sum(w) <= n and sum(t) >= 2 * (n - sum(w)) and sum(t) <= 9 * (n - sum(w))
+    eq = lambda w, t: (w[0] + t[0] / 2) / n
+    pa, pb = eq(wa, ta), eq(wb, tb)
+    sigma = (pa * (1 - pa) / n) ** 0.5
+    assert abs(pa - pb) < 4 * sigma * 2 ** 0.5                                  # difference of two independent estimates
+    assert 0.34 < pa < 0.37                                                    # A-A against eight random hands
+    for counts in (wa[1:], la[1:], ta[1:]):
+        mean = sum(counts) / 8
+        p = mean / n
+        sd = (n * p * (1 - p)) ** 0.5
+        assert max(abs(c - mean) for c in counts) < 5 * sd, counts
+
+
 # ---- showdown (gameplay.clj:118-133) ------------------------------------------------------------------
 def test_showdown_groups(gpu, oracle):
     import ctypes as C
