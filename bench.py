@@ -588,6 +588,38 @@ def run_ours(args):
                           "achieved": rate4 / 32 * MC9_SMEM_WAVEFRONTS_PER_32_TRIALS / 1e12, "peak": world * sms * f_sm4 / 1e12,
                           "unit": "T wavefronts/s", "frac": rate4 / 32 * MC9_SMEM_WAVEFRONTS_PER_32_TRIALS / (world * sms * f_sm4)}}
 
+    # Monte Carlo with a weighted hole range per seat (deal spec R1): six seats on a flop, seat 0 holds A-A, five
+    # seats each draw from a 200-hole weighted range; host call, wall clock (rank-local ranges of the trial index)
+    if rank == 0 or world > 1:
+        import random as _random
+        rnd = _random.Random(7)
+        all_holes = [(a, b) for b in range(52) for a in range(b)]
+        rweights = [None]
+        for _ in range(5):
+            w = [0] * 1326
+            for a, b in rnd.sample(all_holes, 200):
+                w[api.hole_index(a, b)] = rnd.randint(1, 20)
+            rweights.append(w)
+        rholes = [api.mask_of_ids([12, 25])] + [0] * 5
+        rboard = api.mask_of_ids([0, 14, 28])
+        r_trials = 1 << 26
+        rlo, rhi = sharding.shard_range(r_trials, rank, world)
+        api.equity_mc_ranges(rweights, rholes, rboard, 0, SEED, 0, 1 << 16)
+        got_r = [None]
+
+        def ranges_call():
+            w_, t_, l_, v_ = api.equity_mc_ranges(rweights, rholes, rboard, 0, SEED, rlo, rhi - rlo)
+            got_r[0] = torch.tensor(w_ + t_ + l_ + [v_], dtype=torch.int64, device="cuda")
+            if world > 1:
+                dist.all_reduce(got_r[0], op=dist.ReduceOp.SUM)
+        ms_r = wall_region(torch, dist, world, ranges_call, 1, 0)
+        gr = got_r[0].cpu().tolist()
+        work["mc_ranges_6_seats_flop"] = {
+            "trials_per_s": r_trials / (ms_r * 1e-3), "trials": r_trials, "ms": ms_r, "void_trials": gr[-1],
+            "seat0_equity": (gr[0] + gr[6] / 2) / max(1, r_trials - gr[-1]),
+            "counts_sum_ok": all(gr[q] + gr[6 + q] + gr[12 + q] + gr[-1] == r_trials for q in range(6)),
+            "call": "mc_equity_mc_ranges (alias tables built on the host per call; one thread per trial, holes that collide restart the trial)"}
+
     # the reference's own call site: one showdown of a full table through the host ABI (latency-bound by design)
     if rank == 0:
         board9 = api.mask_of_ids([0, 15, 28, 48, 5])
