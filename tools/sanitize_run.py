@@ -20,6 +20,14 @@ want = oracle.eval_batch(masks, 0)
 assert np.array_equal(api.eval7_batch(masks), want)                                        # K1 river image
 assert np.array_equal(api.class_keys()[api.eval_batch_colex32(api.colex_rank(masks))], want)   # unrank + K1 class flavour
 assert np.array_equal(api.eval_batch_packed48(api.pack48(masks)), want)                    # unpack48
+ranks = api.colex_rank(masks)
+assert np.array_equal(api.class_keys()[api.eval_batch_colex27(api.pack27(ranks), len(ranks))], want)   # 27-bit stream
+import torch  # noqa: E402  (device buffers of the caller for the allocation-free call)
+d_r = torch.from_numpy(ranks.view(np.int32).copy()).cuda()
+d_c = torch.empty(len(ranks), dtype=torch.int16, device="cuda")
+E.check(E.lib().mc_eval_batch_colex32_dev_noalloc(d_r.data_ptr(), len(ranks), d_c.data_ptr(), torch.cuda.current_stream().cuda_stream))
+torch.cuda.synchronize()
+assert np.array_equal(api.class_keys()[d_c.cpu().numpy().view(np.uint16)], want)           # static-scratch variant
 flop = oracle.random_hands(1, 0, 20_000, 5)
 assert np.array_equal(api.eval7_batch(flop), oracle.eval_batch(flop, 0))                   # K1 flop / turn image
 mixed = np.concatenate([masks[:500], flop[:500]])
