@@ -132,3 +132,49 @@
         (.setShort in (+ 4 (* 6 i)) (unchecked-short (bit-shift-right h 32)))))
     (check (call-int "mc_eval_batch_packed48" in (long n) out))
     (mapv #(key->value (Integer/toUnsignedLong (.getInt out (* 4 %)))) (range n))))
+
+;; ---- additive: the compact wire format (4-byte colex ranks in, 2-byte class ids out) ---------------------------
+;; mc_eval_batch_colex32: a 7-card hand of the deck travels as the colex rank of its card ids (card.clj:10-13 index),
+;; sum_i C(c_i, i+1) with c_0 < ... < c_6; its value comes back as the index in the ascending list of all 7,462
+;; five-card values, which mc_class_keys hands out once.  Half the bytes of the 6-byte format on the host link.
+(def ^:private suit-index {:hearts 0 :diamonds 1 :spades 2 :clubs 3})
+(defn- card-id [c] (+ (* 13 (suit-index (:suit c))) (- (rank-of c) 2)))
+(defn- choose [n k] (if (< n k) 0 (reduce (fn [acc i] (quot (* acc (- n i)) (inc i))) 1 (range k))))
+(defn colex-rank [cards]
+  (reduce + (map-indexed (fn [i id] (choose id (inc i))) (sort (map card-id cards)))))
+(def ^:private class-values
+  (delay @started
+         (let [m (Memory. (* 4 7462))]
+           (check (call-int "mc_class_keys" m (int 7462)))
+           (mapv #(key->value (Integer/toUnsignedLong (.getInt m (* 4 %)))) (range 7462)))))
+(defn eval-batch-ranks
+  "hands: a seq of 7-card seqs of deck cards -> vector of [cat hit kick] values"
+  [hands]
+  @started
+  (let [hands (vec hands) n (count hands)
+        in (Memory. (* 4 (max n 1))) out (Memory. (* 2 (max n 1)))]
+    (dotimes [i n] (.setInt in (* 4 i) (unchecked-int (colex-rank (hands i)))))
+    (check (call-int "mc_eval_batch_colex32" in (long n) out))
+    (mapv #(@class-values (bit-and 0xFFFF (.getShort out (* 2 %)))) (range n))))
+
+;; ---- additive: end-game in one call (ranking, tie groups, update-stacks; gameplay.clj:122-133) -------------------
+(defn- cards->mask [cards]
+  (reduce bit-or 0 (map #(bit-shift-left 1 (+ (* 16 (quot (card-id %) 13)) (rem (card-id %) 13) 2)) cards)))
+(defn end-game-result
+  "community: 3..5 deck cards; pockets: vector of 2-card seqs by seat; pots: seq of {:bet :n :players #{seat ...}}
+   -> {:values [...] :groups [group index by seat, 0 = best] :delta [chips won by seat]}"
+  [community pockets pots]
+  @started
+  (let [n (count pockets) k (count pots)
+        h (Memory. (* 8 (max n 1))) keys (Memory. 36) grp (Memory. 36) ng (IntByReference.) win (IntByReference.)
+        bet (Memory. (* 8 (max k 1))) cnt (Memory. (* 4 (max k 1))) msk (Memory. (* 4 (max k 1))) delta (Memory. 72)]
+    (.clear delta)
+    (dotimes [i n] (.setLong h (* 8 i) (cards->mask (pockets i))))
+    (doseq [[i p] (map-indexed vector pots)]
+      (.setLong bet (* 8 i) (long (:bet p))) (.setInt cnt (* 4 i) (int (:n p)))
+      (.setInt msk (* 4 i) (int (reduce bit-or 0 (map #(bit-shift-left 1 %) (:players p))))))
+    (check (call-int "mc_end_game" (cards->mask community) h (int n) bet cnt msk (int k) keys grp ng win delta))
+    {:values (mapv #(key->value (Integer/toUnsignedLong (.getInt keys (* 4 %)))) (range n))
+     :groups (mapv #(.getInt grp (* 4 %)) (range n))
+     :delta  (mapv #(.getLong delta (* 8 %)) (range n))}))
+
