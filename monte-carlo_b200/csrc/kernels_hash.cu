@@ -746,6 +746,112 @@ static size_t enum_warp_smem(int n_classes) {
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// K2, pair walk (default).  The per-thread colex walk with its two lowest cards stepped as ONE index: inside
+// a fixed (c2 .. c6) the hands are the C(c2, 2) pairs c0 < c1 < c2 in colex order, i.e. pair index 0, 1, 2, ...  Per hand
+// the thread adds the pair's {rank-key sum, suit counters} (one 8-byte load from the table of all 1,326 pairs) onto the
+// partial hand of its five high cards; only when the pair index reaches C(c2, 2) does the colex walk of the high cards
+// (Walker::bump<2>) run.  The frequent carry of the plain walk (c0 reaching c1, every ~c1 hands per lane, so in 98 % of a
+// warp's steps) is gone: a lane carries every C(c2, 2) hands (~190 on average).  ncu (profiles/r02_k2_pair_ncu.txt): 44
+// executed instructions per hand against 60.5; the first build was then bound by the shared-memory pipe (19.3 wavefronts
+// per 32 hands: pair entry, D, V, key, and a 16-byte category entry), so categories are now counted arithmetically in one
+// 64-bit word of 7-bit fields (15 wavefronts), and thread ranges are dealt round-robin over the blocks (block 0 used to own
+// the slow low indices): 0.404 -> 0.382 -> 0.319 ms for all C(52,7) hands.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(ENUM_THREADS, 1)
+enum7_pair_kernel(uint64_t first, uint64_t count, const HashBlob *__restrict__ g_blob, const CardKey *__restrict__ g_card,
+                  const uint32_t *__restrict__ g_nib, int n_classes, unsigned long long *__restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));            // [LIVE_MAX] by card id; ids >= 52 are zero entries
+    uint2 *pairA = reinterpret_cast<uint2 *>(sdeck + LIVE_MAX);                              // [1326] {rk0 + rk1, sn0 + sn1} by colex pair index
+    uint2 *pairB = pairA + N_PAIRS;                                                   // [1326] {mlo, mhi}
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(pairB + N_PAIRS);   // 16 words
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
+    uint32_t *snib = sbin + BIN_N * BIN_K;
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
+    fill_binom(sbin);
+    for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
+    for (int p = threadIdx.x; p < N_PAIRS; p += blockDim.x) {
+        int c1 = 1;
+        while ((c1 + 1) * c1 / 2 <= p) c1++;                                          // largest c1 with C(c1, 2) <= p
+        const int c0 = p - c1 * (c1 - 1) / 2;
+        const int p0 = c0 + 2 + 3 * (c0 / 13), p1 = c1 + 2 + 3 * (c1 / 13);           // card id -> bit position
+        const uint4 a = live_entry(g_card[p0], p0), b = live_entry(g_card[p1], p1);
+        pairA[p] = make_uint2(a.x + b.x, a.y + b.y);
+        pairB[p] = make_uint2(a.z | b.z, a.w | b.w);
+    }
+    if (threadIdx.x < LIVE_MAX) {
+        const int id = threadIdx.x, p = id + 2 + 3 * (id / 13);
+        sdeck[id] = id < 52 ? live_entry(g_card[p], p) : make_uint4(0, 0, 0, 0);
+    }
+    if (threadIdx.x < 16) sred[threadIdx.x] = 0ull;
+    stage.wait();
+    const uint32_t tbl = staged_table_base(H);
+
+    uint32_t h[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) h[i] = 0;
+    unsigned long long sumN = 0;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t per = (count + nthreads - 1) / nthreads;
+    // ranges are dealt round-robin over the blocks: the slow stretch of the enumeration (low indices: small c2, frequent
+    // carries) is spread over all SMs instead of landing on block 0
+    const uint64_t me = (uint64_t)threadIdx.x * gridDim.x + blockIdx.x;
+    const uint64_t lo = me * per < count ? me * per : count;
+    const uint64_t hi = lo + per < count ? lo + per : count;
+    if (lo < hi) {
+        Walker<7, 1> w;                                              // P[2] = the partial hand of c2 .. c6
+        w.init((uint32_t)(first + lo), 52, sbin, sdeck, HandState{0, SN_BIAS, 0, 0});
+        uint32_t p = (uint32_t)(w.c[0] + w.c[1] * (w.c[1] - 1) / 2);
+        uint32_t pend = (uint32_t)(w.c[2] * (w.c[2] - 1) / 2);
+        HandState Q = w.P[2];
+        for (uint64_t base = lo; base < hi; base += ENUM_FOLD) {
+            const uint32_t len = (uint32_t)(hi - base < (uint64_t)ENUM_FOLD ? hi - base : (uint64_t)ENUM_FOLD);
+            unsigned long long acc = 0;                               // nine 7-bit category counters (<= 32 per fold)
+            uint32_t nsum = 0;                                        // <= 32 * 2^24
+            for (uint32_t j = 0; j < len; j++) {
+                const uint2 A = pairA[p];
+                const uint32_t t = Q.t + A.x, sn = Q.sn + A.y, flag = sn & 0x8888u;
+                uint32_t addr = hb_slot_addr(t, tbl);
+                if (flag) {                                          // one of 0x8, 0x80, 0x800, 0x8000: the flush suit's lane
+                    const uint2 B = pairB[p];
+                    const uint32_t wd = (flag & 0x8800u) ? (Q.mhi | B.y) : (Q.mlo | B.x);
+                    addr = hb_flush_addr(((flag & 0x8080u) ? (wd >> 16) : (wd & 0xFFFFu)) >> 2, tbl);
+                }
+                const uint32_t nib = snib[lds_u16(addr)];             // class codes are dense indices; cat = key >> 20
+                acc += 1ull << (7u * (nib >> 20));                    // (arithmetic: the shared-memory pipe is the busy one)
+                nsum += nib;
+                if (++p == pend) {                                   // every pair below c2 done: colex successor of (c2 .. c6)
+                    w.template bump<2>(sdeck, 52);
+                    Q = w.P[2];
+                    p = 0;
+                    pend = (uint32_t)(w.c[2] * (w.c[2] - 1) / 2);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 9; i++) h[i] += (uint32_t)(acc >> (7 * i)) & 127u;
+            sumN += nsum;
+        }
+    }
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const uint32_t s = warp_sum(h[i]);
+        if (lane == 0 && s) atomicAdd(&sred[i], (unsigned long long)s);
+    }
+    sumN = warp_sum64(sumN);
+    if (lane == 0) atomicAdd(&sred[9], sumN);
+    __syncthreads();
+    if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
+}
+static size_t enum_pair_smem(int n_classes) {
+    return sizeof(HashBlob) + LIVE_MAX * sizeof(uint4) + 2 * N_PAIRS * sizeof(uint2) + 16 * sizeof(unsigned long long) +
+           (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
+}
+
 static size_t enum_smem(int n_classes) {
     return sizeof(HashBlob) + (LIVE_MAX * 32 + 16) * sizeof(uint4) + 16 * sizeof(unsigned long long) +
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
@@ -754,11 +860,21 @@ static size_t enum_smem(int n_classes) {
 cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out,
                               const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (count == 0) return cudaSuccess;
-    // Two walks with identical results.  Default: the per-thread colex walk (0.406 ms for all C(52,7) hands on a B200).
-    // MCP_K2_VARIANT=warp selects the warp-cooperative walk (0.479 ms: its inner loop is 31 instructions per 32 hands
-    // against 41, but run starts, chunk starts and the lanes crossing C(c2, 3) boundaries bring it to 62 executed
-    // instructions per hand at IPC 2.2 -- profiles/r02_k2_warp_ncu.txt); kept as the A/B arm of tools/k2_time.py.
-    static const bool per_thread = [] { const char *e = getenv("MCP_K2_VARIANT"); return !(e && e[0] == 'w'); }();
+    // Three walks with identical results (all C(52,7) hands on a B200; tools/k2_time.py):
+    //   pair (default)          0.319 ms  44 executed instructions per hand, bound by the shared-memory pipe (15 wavefronts per 32 hands)
+    //   MCP_K2_VARIANT=thread   0.404 ms  the plain per-thread colex walk: 60.5 instructions per hand (the c0 / c1 carry diverges 98 % of the steps)
+    //   MCP_K2_VARIANT=warp     0.479 ms  warp-cooperative: 62-68 instructions per hand at IPC 2.2 (profiles/r02_k2_warp_ncu.txt)
+    static const char variant = [] { const char *e = getenv("MCP_K2_VARIANT"); return e ? e[0] : 'p'; }();
+    const bool per_thread = variant != 'w';
+    if (variant == 'p') {
+        const size_t psmem = enum_pair_smem((int)tb.n_classes);
+        cudaError_t e = cudaFuncSetAttribute(enum7_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem);
+        if (e != cudaSuccess) return e;
+        uint64_t want = (count + ENUM_THREADS - 1) / ENUM_THREADS;
+        const int grid = (int)(want > (uint64_t)di.sm_count ? (uint64_t)di.sm_count : want);
+        enum7_pair_kernel<<<grid, ENUM_THREADS, psmem, st>>>(first, count, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, d_out);
+        return cudaGetLastError();
+    }
     if (!per_thread) {
         const size_t wsmem = enum_warp_smem((int)tb.n_classes);
         cudaError_t e = cudaFuncSetAttribute(enum7_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
