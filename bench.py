@@ -32,11 +32,14 @@ ALGO_BYTES_PER_EVAL = 12         # 8 B mask in + 4 B key out
 # thread-level instructions per unit.  SURVEY 8d declared 64 / 70 / 140 / 1024 and allows lowering them "with a SASS
 # count to justify it": these are the executed warp-instructions per unit that ncu measured for the current kernels
 # (profiles/r01_v_k1_v5_ncu_full.txt, profiles/r01_z_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
-OPS = {"eval": 46, "enum": 62, "board2": 69, "mc9": 612}
+OPS = {"eval": 46, "enum": 48, "board2": 69, "mc9": 612}
 # K4 is bound by the shared-memory data pipe (one 128-byte wavefront per SM per clock): ncu counts 186 wavefronts per
 # 32 trials (profiles/r01_k4_768_ncu_full.txt: 141 without bank conflicts -- 13 deck init, 63 deal steps, 42 card
 # entries, 18 hash loads, flush -- plus 45 from the random D / V addresses of a warp sharing banks)
 MC9_SMEM_WAVEFRONTS_PER_32_TRIALS = 186
+# K2 (pair walk) is bound by the same pipe: ncu counts 18.3 wavefronts per 32 enumerated hands (profiles/r02_k2_pair_ncu.txt:
+# the 8-byte pair entry, D, V and the key, all at random addresses of a warp)
+ENUM_SMEM_WAVEFRONTS_PER_32_HANDS = 18.3
 METRIC = "7-card evals/s"
 # SHA-256 of the 27 config-4 counts ("w0,..,w8,t0,..,l8") by log2(trials), recorded from a 1-GPU run of this bench
 # (seed 0x5EED5EED, seat 0 = A-A, eight random seats): any number of ranks must reproduce them
@@ -481,7 +484,10 @@ def run_ours(args):
     work["config2_enumerate_c52_7"] = {
         "hands_per_s": rate2, "ms": ms2 / 10, "histogram_equals_golden": hist == golden7, "sharded_over_ranks": world,
         "roofline": {"bound": "int_issue", "ops_per_unit": OPS["enum"], "achieved": rate2 * OPS["enum"] / 1e12,
-                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate2 * OPS["enum"] / (world * int_peak)}}
+                     "peak": world * int_peak / 1e12, "unit": "Tint-op/s", "frac": rate2 * OPS["enum"] / (world * int_peak)},
+        "roofline_smem": {"bound": "shared-memory wavefronts", "wavefronts_per_32_hands": ENUM_SMEM_WAVEFRONTS_PER_32_HANDS,
+                          "achieved": rate2 / 32 * ENUM_SMEM_WAVEFRONTS_PER_32_HANDS / 1e12, "peak": world * sms * f_sm / 1e12,
+                          "unit": "T wavefronts/s", "frac": rate2 / 32 * ENUM_SMEM_WAVEFRONTS_PER_32_HANDS / (world * sms * f_sm)}}
 
     cnt = torch.zeros(27, dtype=torch.int64, device="cuda")
     holes2 = (C.c_uint64 * 2)(api.mask_of_ids([12, 25]), api.mask_of_ids([37, 50]))
