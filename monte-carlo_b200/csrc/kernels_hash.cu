@@ -1290,39 +1290,42 @@ equity_mc_ranges_kernel(const __grid_constant__ McRangeArgs a, const RangeEntry 
     Tally<MAX_SEATS> tl; tl.clear();
     uint32_t voids = 0;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t tr = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; tr < count; tr += nthreads) {
+    // One ATTEMPT per loop iteration and lane: a lane whose holes collide retries the same trial with the next attempt number
+    // in its next iteration while its neighbours go on to their next trials, so a warp never waits for its unluckiest lane
+    // (with a restart loop per trial the warp ran max-over-lanes attempts, 3-4 instead of 1.3).  (trial, attempt) streams
+    // are what they were: same counts.
+    uint64_t tr = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t attempt = 0;
+    while (tr < count) {
         const uint64_t trial = first + tr;
-        uint64_t hole[MAX_SEATS], used = 0, bm = 0;
-        bool dealt = false;
-        for (uint32_t attempt = 0; attempt < (uint32_t)RANGE_MAX_ATTEMPTS && !dealt; attempt++) {
-            WordStream ws; ws.init(seed_lo, seed_hi, trial, attempt);
-            used = a.used0;
-            bool fail = false;
+        uint64_t hole[MAX_SEATS], used = a.used0, bm = a.board;
+        WordStream ws; ws.init(seed_lo, seed_hi, trial, attempt);
+        bool fail = false;
 #pragma unroll
-            for (int s = 0; s < MAX_SEATS; s++) {
-                if (s < n_seats && !fail) {
-                    hole[s] = a.hole[s];
-                    if (a.rs[s].n) {
-                        const uint32_t slot = ws.below(a.rs[s].n, a.rs[s].zone_n), vv = ws.below(a.rs[s].W, a.rs[s].zone_W);
-                        RangeEntry e = entries[a.rs[s].off + slot];
-                        if (vv >= e.thr) e = entries[a.rs[s].off + e.alias];
-                        const uint64_t h = (1ull << e.c0) | (1ull << e.c1);
-                        fail = (h & used) != 0ull;
-                        used |= h; hole[s] = h;
-                    }
+        for (int s = 0; s < MAX_SEATS; s++) {
+            if (s < n_seats && !fail) {
+                hole[s] = a.hole[s];
+                if (a.rs[s].n) {
+                    const uint32_t slot = ws.below(a.rs[s].n, a.rs[s].zone_n), vv = ws.below(a.rs[s].W, a.rs[s].zone_W);
+                    RangeEntry e = entries[a.rs[s].off + slot];
+                    if (vv >= e.thr) e = entries[a.rs[s].off + e.alias];
+                    const uint64_t h = (1ull << e.c0) | (1ull << e.c1);
+                    fail = (h & used) != 0ull;
+                    used |= h; hole[s] = h;
                 }
             }
-            if (fail) continue;
-            bm = a.board;
-            for (int k = 0; k < need; k++) {
-                for (;;) {
-                    const uint64_t bit = 1ull << slive[ws.below(a.n_live, a.zone_live)];
-                    if (!(used & bit)) { used |= bit; bm |= bit; break; }
-                }
-            }
-            dealt = true;
         }
-        if (!dealt) { voids++; continue; }
+        if (fail) {
+            if (++attempt == (uint32_t)RANGE_MAX_ATTEMPTS) { voids++; tr += nthreads; attempt = 0; }
+            continue;
+        }
+        for (int k = 0; k < need; k++) {
+            for (;;) {
+                const uint64_t bit = 1ull << slive[ws.below(a.n_live, a.zone_live)];
+                if (!(used & bit)) { used |= bit; bm |= bit; break; }
+            }
+        }
+        tr += nthreads; attempt = 0;
         // the board of this trial, then the seats
         HandState b = base;
         {
