@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "hashtab.cuh"
 #include "philox.cuh"
+#include <atomic>
 #include <cstring>
 
 namespace mcp {
@@ -280,23 +281,33 @@ equity_exh_hash_kernel(const __grid_constant__ EqxHashParams prm, const HashBlob
 
 static size_t eqx_smem() { return sizeof(HashBlob) + LIVE_MAX * sizeof(uint4) + BIN_N * BIN_K * sizeof(uint32_t); }
 
+// (host helpers of the launchers: they walk the set bits only -- a heads-up launch is a few microseconds of device time, so
+// the host side of the call counts)
 static void fill_live(uint64_t live_mask, const CardKey *card, uint4 *live, int *n_live) {
     int nl = 0;
-    for (int b = 0; b < 64; b++) if ((live_mask >> b) & 1ull) live[nl++] = live_entry(card[b], b);
+    for (uint64_t x = live_mask; x; x &= x - 1) { const int b = __builtin_ctzll(x); live[nl++] = live_entry(card[b], b); }
     *n_live = nl;
     for (int i = nl; i < LIVE_MAX; i++) live[i] = make_uint4(0, 0, 0, 0);
 }
 static HandState state_of(uint64_t mask, const CardKey *card, uint32_t sn0) {
     HandState h{0, sn0, (uint32_t)mask, (uint32_t)(mask >> 32)};
-    for (int b = 0; b < 64; b++) if ((mask >> b) & 1ull) { h.t += card[b].rk; h.sn += card[b].sn; }
+    for (uint64_t x = mask; x; x &= x - 1) { const int b = __builtin_ctzll(x); h.t += card[b].rk; h.sn += card[b].sn; }
     return h;
 }
 
 template <int K, int NS, bool EV>
 static cudaError_t launch_eqx(const EqxHashParams &prm, const HashBlob *blob, long long *d_counts, int grid, cudaStream_t st) {
     auto kern = equity_exh_hash_kernel<K, NS, EV>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
+    // the attribute is per function and device: set once per (instantiation, device), not on every launch
+    static std::atomic<uint64_t> attr_done{0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
+    if (dev >= 64 || !((attr_done.load(std::memory_order_relaxed) >> dev) & 1ull)) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)eqx_smem());
+        if (e != cudaSuccess) return e;
+        if (dev < 64) attr_done.fetch_or(1ull << dev, std::memory_order_relaxed);
+    }
     kern<<<grid, eqx_threads<NS>(), eqx_smem(), st>>>(prm, blob, d_counts);
     return cudaGetLastError();
 }
