@@ -863,6 +863,146 @@ static size_t enum_pair_smem(int n_classes) {
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// K2, lockstep walk (default for large ranges).  The pair walk's biggest shared-memory cost is the pair entry itself: 32
+// lanes at 32 unrelated pair indices cost ~8 wavefronts per LDS.64.  Here all lanes of a warp share c2 and step the pair
+// index p = 0 .. C(c2, 2) - 1 TOGETHER, each lane on its own four high cards (c3 < c4 < c5 < c6 above c2): the pair entry
+// is one broadcast load.  A unit of work is (c2, 32 consecutive four-card tops in colex order over the cards above c2, a
+// chunk of at most 64 pair indices): a warp's whole share is ~880 hand-steps, so whole pair runs (up to 1,081 steps) would
+// leave the grid badly balanced; units are dealt round-robin over all warps of the grid.  The enumeration ORDER is therefore not the colex order -- the outputs are sums, any order gives the
+// same histogram and checksum -- but index ranges are still honoured: a hand's colex index is base(c2 .. c6) + p, the
+// kernel only visits tops whose c6 the range can contain and counts a hand only if its index lies in [first, first + count).
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t EL_PCHUNK = 64;
+template <bool FULL>
+__global__ void __launch_bounds__(ENUM_THREADS, 1)
+enum7_lock_kernel(uint32_t first, uint32_t count, int c6lo, int c6hi, const HashBlob *__restrict__ g_blob,
+                  const CardKey *__restrict__ g_card, const uint32_t *__restrict__ g_nib, int n_classes,
+                  unsigned long long *__restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    HashBlob *H = reinterpret_cast<HashBlob *>(smem_raw);
+    uint4 *sdeck = reinterpret_cast<uint4 *>(smem_raw + sizeof(HashBlob));            // [LIVE_MAX] by card id
+    uint2 *pairA = reinterpret_cast<uint2 *>(sdeck + LIVE_MAX);                       // [1326] {rk0 + rk1, sn0 + sn1} by colex pair index
+    uint2 *pairB = pairA + N_PAIRS;                                                   // [1326] {mlo, mhi}
+    unsigned long long *sred = reinterpret_cast<unsigned long long *>(pairB + N_PAIRS);   // 16 words
+    uint32_t *sbin = reinterpret_cast<uint32_t *>(sred + 16);
+    uint32_t *snib = sbin + BIN_N * BIN_K;
+    __shared__ uint32_t sfirst[64], sqlo[64], sqhi[64];                               // by c2: first unit, first / last + 1 top index
+    __shared__ unsigned long long mbar;
+    BulkStage stage;
+    stage.start(&mbar, H, g_blob, (uint32_t)sizeof(HashBlob));
+    fill_binom(sbin);
+    for (int i = threadIdx.x; i < n_classes; i += blockDim.x) snib[i] = g_nib[i];
+    for (int p = threadIdx.x; p < N_PAIRS; p += blockDim.x) {
+        int c1 = 1;
+        while ((c1 + 1) * c1 / 2 <= p) c1++;                                          // largest c1 with C(c1, 2) <= p
+        const int c0 = p - c1 * (c1 - 1) / 2;
+        const int p0 = c0 + 2 + 3 * (c0 / 13), p1 = c1 + 2 + 3 * (c1 / 13);           // card id -> bit position
+        const uint4 a = live_entry(g_card[p0], p0), b = live_entry(g_card[p1], p1);
+        pairA[p] = make_uint2(a.x + b.x, a.y + b.y);
+        pairB[p] = make_uint2(a.z | b.z, a.w | b.w);
+    }
+    if (threadIdx.x < LIVE_MAX) {
+        const int id = threadIdx.x, p = id + 2 + 3 * (id / 13);
+        sdeck[id] = id < 52 ? live_entry(g_card[p], p) : make_uint4(0, 0, 0, 0);
+    }
+    if (threadIdx.x < 16) sred[threadIdx.x] = 0ull;
+    stage.wait();
+    const uint32_t tbl = staged_table_base(H);
+    // tops per c2: d3 < d4 < d5 < d6 over the 51 - c2 cards above c2 (c_i = c2 + 1 + d_i), colex index q; a range can only
+    // hold hands whose c6 lies in [c6lo, c6hi]: q in [C(c6lo - c2 - 1, 4), C(c6hi - c2, 4))
+    if (threadIdx.x < 64) {
+        const int c2 = threadIdx.x;
+        uint32_t lo = 0, hi = 0;
+        if (c2 >= 2 && c2 <= 47) {
+            const int dl = c6lo - c2 - 1, dh = c6hi - c2;
+            lo = dl > 0 ? sbin[dl * BIN_K + 4] : 0u;
+            hi = dh > 0 ? sbin[(dh > 51 - c2 ? 51 - c2 : dh) * BIN_K + 4] : 0u;
+            if (hi < lo) hi = lo;
+        }
+        sqlo[c2] = lo; sqhi[c2] = hi;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int c2 = 0; c2 < 64; c2++) {
+            sfirst[c2] = (c2 >= 2 && c2 <= 47) ? run : (c2 < 2 ? 0u : 0xFFFFFFFFu);
+            if (c2 >= 2 && c2 <= 47) run += ((sqhi[c2] - sqlo[c2] + 31u) >> 5) * (((uint32_t)(c2 * (c2 - 1) / 2) + EL_PCHUNK - 1u) / EL_PCHUNK);
+        }
+        sfirst[48] = run;                                                             // total number of units; 49.. stay 2^32 - 1
+    }
+    __syncthreads();
+    const uint32_t n_units = sfirst[48];
+
+    uint32_t h[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) h[i] = 0;
+    unsigned long long sumN = 0;
+    const int lane = threadIdx.x & 31;
+    const uint32_t nw = gridDim.x * (ENUM_THREADS / 32), gw = blockIdx.x * (ENUM_THREADS / 32) + (threadIdx.x >> 5);
+    for (uint32_t unit = gw; unit < n_units; unit += nw) {
+        // c2 of the unit: the largest c2 <= 47 with sfirst[c2] <= unit (units of empty c2 have zero width and are skipped by
+        // taking the largest)
+        uint32_t c2 = 2;
+#pragma unroll
+        for (uint32_t step = 32; step >= 1; step >>= 1) { const uint32_t y = c2 + step; if (y <= 47u && sfirst[y] <= unit) c2 = y; }
+        const uint32_t qend = sqhi[c2];
+        const uint32_t npairs = c2 * (c2 - 1u) / 2u, nchunks = (npairs + EL_PCHUNK - 1u) / EL_PCHUNK;
+        const uint32_t u = unit - sfirst[c2], qb = u / nchunks, p0 = (u - qb * nchunks) * EL_PCHUNK, p1 = min(npairs, p0 + EL_PCHUNK);
+        uint32_t q = sqlo[c2] + (qb << 5) + (uint32_t)lane;
+        const bool valid = q < qend;
+        q = valid ? q : qend - 1u;                                                    // (an idle lane walks a valid top, uncounted)
+        int d[4];
+        colex_unrank<4>(q, 0, sbin, d);
+        const int c3 = d[0] + (int)c2 + 1, c4 = d[1] + (int)c2 + 1, c5 = d[2] + (int)c2 + 1, c6 = d[3] + (int)c2 + 1;
+        const uint4 e2 = sdeck[c2], e3 = sdeck[c3], e4 = sdeck[c4], e5 = sdeck[c5], e6 = sdeck[c6];
+        const HandState Q{e2.x + e3.x + e4.x + e5.x + e6.x, SN_BIAS + e2.y + e3.y + e4.y + e5.y + e6.y,
+                          e2.z | e3.z | e4.z | e5.z | e6.z, e2.w | e3.w | e4.w | e5.w | e6.w};
+        // colex index of the hand with pair index p: base + p
+        const uint32_t base = sbin[c6 * BIN_K + 7] + sbin[c5 * BIN_K + 6] + sbin[c4 * BIN_K + 5] + sbin[c3 * BIN_K + 4] + sbin[c2 * BIN_K + 3];
+        const uint32_t rel = base - first;                                            // (wraps below the range: then rel + p >= count)
+        if (!FULL) {
+            // does [base, base + npairs) meet [first, first + count) for any lane?  (all below 2^28: no wrap)
+            const bool overlap = valid && base + p0 < first + count && base + p1 > first;
+            if (!__any_sync(0xFFFFFFFFu, overlap)) continue;
+        }
+        unsigned long long acc = 0;                                   // nine 7-bit category counters (<= 32 per fold)
+        uint32_t nsum = 0;                                            // <= 32 * 2^24
+        for (uint32_t p = p0; p < p1; p++) {
+            const uint2 A = pairA[p];                                 // the same entry for every lane: one broadcast
+            const uint32_t t = Q.t + A.x, sn = Q.sn + A.y, flag = sn & 0x8888u;
+            uint32_t addr = hb_slot_addr(t, tbl);
+            if (flag) {                                              // one of 0x8, 0x80, 0x800, 0x8000: the flush suit's lane
+                const uint2 B = pairB[p];
+                const uint32_t wd = (flag & 0x8800u) ? (Q.mhi | B.y) : (Q.mlo | B.x);
+                addr = hb_flush_addr(((flag & 0x8080u) ? (wd >> 16) : (wd & 0xFFFFu)) >> 2, tbl);
+            }
+            const uint32_t nib = snib[lds_u16(addr)];                 // class codes are dense indices; cat = key >> 20
+            const bool ok = valid && (FULL || rel + p < count);
+            acc += (unsigned long long)ok << (7u * (nib >> 20));
+            nsum += ok ? nib : 0u;
+            if ((p & 31u) == 31u) {
+#pragma unroll
+                for (int i = 0; i < 9; i++) h[i] += (uint32_t)(acc >> (7 * i)) & 127u;
+                sumN += nsum;
+                acc = 0; nsum = 0;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 9; i++) h[i] += (uint32_t)(acc >> (7 * i)) & 127u;
+        sumN += nsum;
+    }
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const uint32_t s = warp_sum(h[i]);
+        if (lane == 0 && s) atomicAdd(&sred[i], (unsigned long long)s);
+    }
+    sumN = warp_sum64(sumN);
+    if (lane == 0) atomicAdd(&sred[9], sumN);
+    __syncthreads();
+    if (threadIdx.x < 10 && sred[threadIdx.x]) atomicAdd(&out[threadIdx.x], sred[threadIdx.x]);
+}
+
 static size_t enum_smem(int n_classes) {
     return sizeof(HashBlob) + (LIVE_MAX * 32 + 16) * sizeof(uint4) + 16 * sizeof(unsigned long long) +
            (BIN_N * BIN_K + (size_t)n_classes) * sizeof(uint32_t);
@@ -875,9 +1015,22 @@ cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long
     //   pair (default)          0.319 ms  44 executed instructions per hand, bound by the shared-memory pipe (15 wavefronts per 32 hands)
     //   MCP_K2_VARIANT=thread   0.404 ms  the plain per-thread colex walk: 60.5 instructions per hand (the c0 / c1 carry diverges 98 % of the steps)
     //   MCP_K2_VARIANT=warp     0.479 ms  warp-cooperative: 62-68 instructions per hand at IPC 2.2 (profiles/r02_k2_warp_ncu.txt)
-    static const char variant = [] { const char *e = getenv("MCP_K2_VARIANT"); return e ? e[0] : 'p'; }();
+    //   lockstep                see enum7_lock_kernel: the default for ranges of at least 2^22 hands (MCP_K2_VARIANT=lock forces it)
+    static const char variant = [] { const char *e = getenv("MCP_K2_VARIANT"); return e ? e[0] : 'a'; }();      // 'a' = automatic
     const bool per_thread = variant != 'w';
-    if (variant == 'p') {
+    if (variant == 'l' || (variant == 'a' && count >= ((uint64_t)1 << 22))) {
+        const size_t lsmem = enum_pair_smem((int)tb.n_classes);
+        const uint64_t total = cbinom(52, 7);
+        const bool full = first == 0 && count == total;
+        auto c6_of = [](uint64_t idx) { int x = 6; while (x < 51 && cbinom(x + 1, 7) <= idx) x++; return x; };
+        const int c6lo = full ? 0 : c6_of(first), c6hi = full ? 51 : c6_of(first + count - 1);
+        auto kern = full ? enum7_lock_kernel<true> : enum7_lock_kernel<false>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lsmem);
+        if (e != cudaSuccess) return e;
+        kern<<<di.sm_count, ENUM_THREADS, lsmem, st>>>((uint32_t)first, (uint32_t)count, c6lo, c6hi, tb.d_blob, tb.d_card, tb.d_nib, (int)tb.n_classes, d_out);
+        return cudaGetLastError();
+    }
+    if (variant == 'p' || variant == 'a') {
         const size_t psmem = enum_pair_smem((int)tb.n_classes);
         cudaError_t e = cudaFuncSetAttribute(enum7_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem);
         if (e != cudaSuccess) return e;

@@ -26,4 +26,4 @@ for rep in range(20):
 o = out.tolist()
 GOLD = [23620800, 58877280, 31456080, 6466680, 5576460, 4051784, 3473184, 224848, 37444]
 print("K2 (%s walk): %.4f ms = %.1f G hands/s, golden histogram %s, key sum %s" % (
-    {"w": "warp-cooperative", "t": "per-thread"}.get(os.environ.get("MCP_K2_VARIANT", "")[:1], "pair"), best, 133784560 / best / 1e6, o[:9] == GOLD, o[9] == 307406628956200))
+    {"w": "warp-cooperative", "t": "per-thread", "p": "pair"}.get(os.environ.get("MCP_K2_VARIANT", "")[:1], "lockstep"), best, 133784560 / best / 1e6, o[:9] == GOLD, o[9] == 307406628956200))
