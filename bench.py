@@ -32,14 +32,15 @@ ALGO_BYTES_PER_EVAL = 12         # 8 B mask in + 4 B key out
 # thread-level instructions per unit.  SURVEY 8d declared 64 / 70 / 140 / 1024 and allows lowering them "with a SASS
 # count to justify it": these are the executed warp-instructions per unit that ncu measured for the current kernels
 # (profiles/r01_v_k1_v5_ncu_full.txt, profiles/r01_z_k2_k5_ncu_full.txt), so frac = share of the 128-lane issue peak
-OPS = {"eval": 46, "enum": 48, "board2": 69, "mc9": 612}
+OPS = {"eval": 46, "enum": 35, "board2": 69, "mc9": 612}
 # K4 is bound by the shared-memory data pipe (one 128-byte wavefront per SM per clock): ncu counts 186 wavefronts per
 # 32 trials (profiles/r01_k4_768_ncu_full.txt: 141 without bank conflicts -- 13 deck init, 63 deal steps, 42 card
 # entries, 18 hash loads, flush -- plus 45 from the random D / V addresses of a warp sharing banks)
 MC9_SMEM_WAVEFRONTS_PER_32_TRIALS = 186
-# K2 (pair walk) is bound by the same pipe: ncu counts 18.3 wavefronts per 32 enumerated hands (profiles/r02_k2_pair_ncu.txt:
-# the 8-byte pair entry, D, V and the key, all at random addresses of a warp)
-ENUM_SMEM_WAVEFRONTS_PER_32_HANDS = 18.3
+# K2 (lockstep walk) is bound by the same pipe: ncu counts 12.9 wavefronts per 32 enumerated hands (profiles/r02_k2_lock_ncu.txt:
+# D, V and the key at random addresses of a warp, the pair entry as one broadcast; a rank's share of a sharded run goes through the
+# same kernel as long as it holds at least 2^22 hands)
+ENUM_SMEM_WAVEFRONTS_PER_32_HANDS = 12.9
 METRIC = "7-card evals/s"
 # SHA-256 of the 27 config-4 counts ("w0,..,w8,t0,..,l8") by log2(trials), recorded from a 1-GPU run of this bench
 # (seed 0x5EED5EED, seat 0 = A-A, eight random seats): any number of ranks must reproduce them

@@ -1011,8 +1011,9 @@ static size_t enum_smem(int n_classes) {
 cudaError_t launch_enum7_hash(uint64_t first, uint64_t count, unsigned long long *d_out,
                               const DeviceTables &tb, const DeviceInfo &di, cudaStream_t st) {
     if (count == 0) return cudaSuccess;
-    // Three walks with identical results (all C(52,7) hands on a B200; tools/k2_time.py):
-    //   pair (default)          0.319 ms  44 executed instructions per hand, bound by the shared-memory pipe (15 wavefronts per 32 hands)
+    // Four walks with identical results (all C(52,7) hands on a B200; tools/k2_time.py):
+    //   lockstep (>= 2^22 hands) 0.235 ms  35 executed instructions and 12.9 shared-memory wavefronts per hand (profiles/r02_k2_lock_ncu.txt)
+    //   pair (smaller ranges)   0.317 ms  44 executed instructions per hand, bound by the shared-memory pipe (15 wavefronts per 32 hands)
     //   MCP_K2_VARIANT=thread   0.404 ms  the plain per-thread colex walk: 60.5 instructions per hand (the c0 / c1 carry diverges 98 % of the steps)
     //   MCP_K2_VARIANT=warp     0.479 ms  warp-cooperative: 62-68 instructions per hand at IPC 2.2 (profiles/r02_k2_warp_ncu.txt)
     //   lockstep                see enum7_lock_kernel: the default for ranges of at least 2^22 hands (MCP_K2_VARIANT=lock forces it)
